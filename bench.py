@@ -1,0 +1,340 @@
+#!/usr/bin/env python
+"""bench.py -- cell-updates/s of batched 64x64-torus Life stepping (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one pass of the hot path over one batch: BASELINE config 2, 1 Mi seeded random soups
+stepped 1024 generations in registers (per GPU; weak scaling: every rank owns its own 1 Mi ids).
+  value     Gcell/s, inputs resident in HBM, CUDA events on the launching stream, max over ranks
+  e2e       same metric through lifeb200_step_batch_host with PINNED HOST buffers (H2D + D2H timed)
+  roofline  integer (ALU) pipe: achieved lane-instr/s = cells/s x 0.375 (2 SHF + 10 LOP3
+            per 32 cells per generation) vs the LOP3 rate measured in the same run; plus the
+            HBM-bound G=1 launch vs MEASURED_PEAKS.json
+  cpu_baseline  the reference's own LifeState::Step(n) (oracle/_ref) on all host cores, bounded sample
+torch is used for torch.distributed (NCCL barrier / max / hit-counter gather) only.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SEED = 0x4C696665415049
+N_SOUPS = 1 << 20
+GENS = 1024
+INSTR_PER_CELL = 12.0 / 32.0
+METRIC = "cell_updates_per_sec"
+UNIT = "Gcell/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--soups", type=int, default=N_SOUPS, help="soups per GPU (default: BASELINE config 2)")
+    ap.add_argument("--gens", type=int, default=GENS)
+    ap.add_argument("--lpp", type=int, default=0, help="lanes per pattern override (tuning)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(args, world):
+    return {"workload": f"config2: {args.soups} random 64x64 soups/GPU x {args.gens} generations in-register "
+                        f"(splitmix64 seed 0x{SEED:X}, full-density)",
+            "soups_per_gpu": args.soups, "generations": args.gens, "pattern_bytes": 512,
+            "parallelism": f"batch-sharded x{world} (no data-path collective; counters gathered)",
+            "l2_policy": f"inputs larger than L2 ({args.soups * 512 >> 20} MiB in + same out per step, out of place)"}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own Step(n) on the host cores (oracle/_ref), else the C port
+# ------------------------------------------------------------------------------------------------
+def load_cpu_checker():
+    from oracle.loader import Port, Ref
+    ref = Ref.load()
+    return ref if ref is not None else Port()
+
+
+def cpu_time_sample(chk, soups, gens, threads):
+    t0 = time.perf_counter()
+    chk.step_batch(soups, gens, threads)
+    return time.perf_counter() - t0
+
+
+def cpu_baseline(gens, target_s=10.0):
+    from oracle.loader import Port
+    chk = load_cpu_checker()
+    threads = chk.threads()
+    port = Port()
+    cal_n = 256 * max(1, threads)
+    soups = port.soup(0, cal_n, SEED, 0)
+    dt = cpu_time_sample(chk, soups, gens, threads)
+    rate = cal_n / max(dt, 1e-6)
+    n = int(min(max(rate * target_s, cal_n), 1 << 18))
+    soups = port.soup(0, n, SEED, 0)
+    dt = cpu_time_sample(chk, soups, gens, threads)
+    cells = n * 4096.0 * gens
+    return {"value": cells / dt / 1e9, "unit": UNIT, "cores": threads, "kind": chk.kind,
+            "sample": f"{n} of the same seeded soups x {gens} generations, contiguous chunks over {threads} threads, "
+                      f"{dt:.1f} s wall" + (f", isa {chk.isa()}" if hasattr(chk, "isa") else "")}
+
+
+def run_reference_arm(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path, all host threads, rank 0 only."""
+    if rank != 0:
+        return
+    from oracle.loader import Port
+    chk = load_cpu_checker()
+    threads = chk.threads()
+    port = Port()
+    total_steps = args.steps + args.warmup
+    per_step_s = max(1.0, min(15.0, 90.0 / max(1, total_steps)))
+    cal_n = 128 * max(1, threads)
+    soups = port.soup(0, cal_n, SEED, 0)
+    dt = cpu_time_sample(chk, soups, args.gens, threads)
+    n = int(min(max(cal_n / max(dt, 1e-6) * per_step_s, cal_n), args.soups))
+    soups = port.soup(0, n, SEED, 0)
+    for _ in range(args.warmup):
+        cpu_time_sample(chk, soups, args.gens, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        chk.step_batch(soups, args.gens, threads)
+    dt = time.perf_counter() - t0
+    cells = n * 4096.0 * args.gens * args.steps
+    value = cells / dt / 1e9
+    sample = (f"each step = {n} of the workload's seeded soups x {args.gens} generations on {threads} host threads "
+              f"(bounded sample of the {args.soups}-soup batch)")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": workload_config(args, world),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": chk.kind, "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (NVML), runs during the timed region
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self.ok = [], set(), None, False
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:  # noqa: BLE001
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if r & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:  # noqa: BLE001
+                pass
+            self._stop.wait(0.02)
+
+    def start(self):
+        if self.ok:
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thread:
+            self._thread.join()
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": getattr(self, "err", "no samples")}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from lifeapi_b200 import HIT_DTYPE, Engine, gather_hits
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    distributed = world > 1
+    if distributed:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if not distributed:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    eng = Engine(local_rank)
+    if args.lpp:
+        eng.set_lanes_per_pattern(args.lpp)
+    info = eng.device_info()
+    n, gens = args.soups, args.gens
+    first_id = rank * n
+    nbytes = n * 512
+    d_in, d_out = eng.malloc(nbytes), eng.malloc(nbytes)
+    eng.soup_dev(d_in, first_id, n, SEED, 0)
+    eng.sync()
+
+    # ---- integer-pipe peak, measured on this box in this run ----------------------------------
+    p_int, mhz_eff = eng.measure_int_peak()
+
+    def one_step():
+        eng.step_batch_dev(d_in, d_out, n, gens)
+
+    for _ in range(args.warmup):
+        one_step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    l0 = eng.launch_count()
+    barrier()
+    eng.timer_start()
+    for _ in range(args.steps):
+        one_step()
+    ms = eng.timer_stop()
+    barrier()
+    launches = eng.launch_count() - l0
+    clocks = sampler.stop()
+    ms = max_over_ranks(ms)
+    cells_per_step_all = float(world) * n * 4096.0 * gens
+    value = cells_per_step_all * args.steps / (ms * 1e-3) / 1e9
+    kernel_ms = ms / args.steps
+
+    # ---- counters / checksum gathered over NCCL (the path's only collective) --------
+    pop_sum, hash_xor = eng.fold_dev(d_out, n, first_id)
+    if distributed:
+        _, sums, xors = gather_hits(np.zeros(0, dtype=HIT_DTYPE), [pop_sum, hash_xor], device=dev)
+        pop_sum, hash_xor = sums[0], xors[1]
+
+    # ---- HBM-bound companion: one generation per launch (load/store phases dominate) -----------
+    for _ in range(3):
+        eng.step_batch_dev(d_in, d_out, n, 1)
+    eng.sync()
+    eng.timer_start()
+    reps1 = 10
+    for _ in range(reps1):
+        eng.step_batch_dev(d_in, d_out, n, 1)
+    ms1 = eng.timer_stop() / reps1
+    hbm_gbs = 2.0 * nbytes / (ms1 * 1e-3) / 1e9
+
+    # ---- e2e: host buffers through the C ABI, copies inside the timed region -------------------
+    e2e = None
+    if not args.no_e2e:
+        h_in = eng.host_alloc((n, 64))
+        h_out = eng.host_alloc((n, 64))
+        eng.d2h(h_in, d_in)
+        eng.sync()
+        for _ in range(min(args.warmup, 2)):
+            eng.step_batch_host(h_in, gens, out=h_out)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            eng.step_batch_host(h_in, gens, out=h_out)
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        # result check: the host path's output equals the resident path's (same checksum)
+        eng.h2d(d_out, h_out)
+        chk = eng.fold_dev(d_out, n, first_id)
+        e2e = {"value": cells_per_step_all * args.steps / dt / 1e9, "unit": UNIT, "h2d_bytes_per_step": nbytes * world,
+               "d2h_bytes_per_step": nbytes * world, "ms_per_step": dt / args.steps * 1e3,
+               "host_memory": "pinned (lifeb200_host_alloc)", "api": "lifeb200_step_batch_host",
+               "matches_resident_path": bool(distributed or chk == (pop_sum, hash_xor))}
+        eng.host_free(h_in)
+        eng.host_free(h_out)
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:  # noqa: BLE001
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    hbm_src = "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+
+    per_gpu_cells_s = n * 4096.0 * gens / (kernel_ms * 1e-3)
+    achieved = per_gpu_cells_s * INSTR_PER_CELL
+    roofline = {"bound": "int_pipe", "achieved": achieved / 1e12, "peak": p_int / 1e12, "unit": "T lane-instr/s (LOP3+SHF)",
+                "frac": achieved / p_int, "traffic": None,
+                "kernel": "step_kernel<LPP>", "kernel_ms": kernel_ms,
+                "algorithmic": "12 int-pipe instr per 32 cells per generation = 0.375 instr/cell-update (SURVEY 8d)",
+                "peak_source": f"LOP3 microbenchmark in this run (lifeb200_measure_int_peak): {p_int / 1e12:.2f} T/s = "
+                               f"{info['sm_count']} SMs x 64 lanes x {mhz_eff:.0f} MHz effective",
+                "hbm": {"bound": "hbm", "achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak,
+                        "what": "same kernel at 1 generation per launch (512 B in + 512 B out per pattern)",
+                        "ms": ms1, "peak_source": hbm_src, "traffic": None}}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_baseline(gens)
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": kernel_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
+                "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e,
+                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+                "checksum": {"pop_sum": int(pop_sum), "hash_xor": f"{int(hash_xor):016x}"},
+                "lanes_per_pattern": args.lpp or "default", "device": {"sms": info["sm_count"], "cc": list(info["cc"])}}
+        print(json.dumps(line), flush=True)
+
+    eng.free(d_in)
+    eng.free(d_out)
+    eng.close()
+    if distributed:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

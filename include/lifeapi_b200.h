@@ -1,0 +1,142 @@
+/* lifeapi_b200.h -- C ABI of the B200-native batched stepping engine for LifeAPI.
+ *
+ * The reference (scorbiclife/LifeAPI @ 4e9bb99) has no FFI layer: its API is the header
+ * LifeAPI.hpp.  These entry points are what a drop-in replacement header binds for the stepping
+ * path (see include/LifeAPI_b200.hpp and INTEGRATION.md).  Each function cites the reference
+ * interface it replaces.  Plain pointers and sizes only; no torch / C++ types.
+ *
+ * Conventions
+ *   pattern   = 64 little-endian uint64_t = 512 bytes; word i = column x=i, bit j = row y=j
+ *               (LifeAPI.hpp:39-40,131).  A batch is a flat array of patterns (== LifeState[]).
+ *   return    = 0 on success, non-zero on failure (LIFEB200_E_*); lifeb200_last_error() gives
+ *               the message for the calling thread.  The reference has no recoverable errors
+ *               (SURVEY.md 8b), so header wrappers abort on non-zero.
+ *   *_dev     = pointers are DEVICE pointers on the context's GPU; work is enqueued on the
+ *               context's stream and is asynchronous; call lifeb200_sync().
+ *   *_host    = pointers are HOST pointers; the call stages through pinned buffers, overlaps
+ *               copy and compute, and returns when the result is in the caller's buffer.
+ *   There is no CPU fallback: without a usable CUDA device every compute call fails.
+ */
+#ifndef LIFEAPI_B200_H
+#define LIFEAPI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LIFEB200_ABI_VERSION 1
+#define LIFEB200_WORDS 64          /* LifeAPI.hpp:12  const int N = 64 */
+#define LIFEB200_PATTERN_BYTES 512 /* sizeof(LifeState) */
+
+enum {
+  LIFEB200_OK = 0,
+  LIFEB200_E_CUDA = 1,      /* CUDA runtime error (message has the cudaError string) */
+  LIFEB200_E_ARG = 2,       /* bad argument (null / misaligned pointer, bad enum) */
+  LIFEB200_E_OVERFLOW = 3,  /* hit buffer too small: *n_hits holds the required count */
+  LIFEB200_E_NODEVICE = 4   /* no CUDA device / wrong architecture */
+};
+
+typedef struct lifeb200_ctx lifeb200_ctx; /* opaque: device, stream, scratch, pinned staging */
+
+/* ---- context / device management ------------------------------------------------------- */
+int lifeb200_abi_version(void);
+const char* lifeb200_last_error(void);
+int lifeb200_device_count(int* count);
+int lifeb200_create(int device, lifeb200_ctx** out);
+int lifeb200_destroy(lifeb200_ctx* ctx);
+/* Use an externally owned cudaStream_t (e.g. torch's current stream); NULL restores the own one. */
+int lifeb200_set_stream(lifeb200_ctx* ctx, void* cuda_stream);
+int lifeb200_sync(lifeb200_ctx* ctx);
+int lifeb200_device_info(lifeb200_ctx* ctx, int* sm_count, int* cc_major, int* cc_minor, int* clock_khz,
+                         size_t* total_mem);
+/* Choose the lane-group width of the step kernels: lanes per pattern in {1,2,4,8,16,32};
+ * 0 restores the default.  Results never depend on it. */
+int lifeb200_set_lanes_per_pattern(lifeb200_ctx* ctx, int lpp);
+
+/* ---- memory ---------------------------------------------------------------------------- */
+int lifeb200_malloc(lifeb200_ctx* ctx, void** dptr, size_t bytes);
+int lifeb200_free(lifeb200_ctx* ctx, void* dptr);
+int lifeb200_host_alloc(lifeb200_ctx* ctx, void** hptr, size_t bytes); /* pinned */
+int lifeb200_host_free(lifeb200_ctx* ctx, void* hptr);
+int lifeb200_memcpy_h2d(lifeb200_ctx* ctx, void* dst, const void* src, size_t bytes); /* async */
+int lifeb200_memcpy_d2h(lifeb200_ctx* ctx, void* dst, const void* src, size_t bytes); /* async */
+int lifeb200_memset(lifeb200_ctx* ctx, void* dst, int value, size_t bytes);           /* async */
+
+/* ---- timing on the context's stream (CUDA events) -------------------------------------- */
+int lifeb200_timer_start(lifeb200_ctx* ctx);
+int lifeb200_timer_stop(lifeb200_ctx* ctx, float* elapsed_ms); /* records, syncs, returns ms */
+/* Number of kernels this library launched on ctx since creation. */
+int lifeb200_launch_count(lifeb200_ctx* ctx, uint64_t* launches);
+
+/* ---- A4/A5  LifeState::Step(), Step(unsigned)  (LifeAPI.hpp:866,877-881,1196-1216) ------ */
+/* out[p] = in[p] stepped `gens` generations, for p < n.  in == out is allowed. gens may be 0. */
+int lifeb200_step_batch_dev(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n, unsigned gens);
+int lifeb200_step_batch_host(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n, unsigned gens);
+
+/* ---- A14  soup source (replaces RandomState, LifeAPI.hpp:63-69, with a seeded generator) - */
+/* word(p,i) = splitmix64(seed + 64*(first_id+p) + i); dist 0 = full 64-bit words,
+ * dist 1 = the reference-shaped draw uniform in [2^61, 2^62] (LifeAPI.hpp:21-22). */
+int lifeb200_soup_dev(lifeb200_ctx* ctx, uint64_t* out, uint64_t first_id, size_t n, uint64_t seed, int dist);
+
+/* ---- A8  NeighbourCount(const LifeState&) / CountNeighbourhood --------------------------
+ * (NeighbourCount.hpp:40-70, LifeAPI.hpp:909-952).  planes[p] = 4 x 64 words in the member
+ * order bit3, bit2, bit1, bit0 (NeighbourCount.hpp:7-11): 3x3 sum INCLUDING the centre. */
+int lifeb200_neighbour_count_dev(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n);
+int lifeb200_neighbour_count_host(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n);
+
+/* ---- A11/A12  fused step + LifeState::Contains(const LifeTarget&) (LifeTarget.hpp:44-51) - */
+typedef struct lifeb200_hit {
+  uint64_t id;             /* pattern / placement id */
+  uint32_t g_first_false;  /* first generation g>=1 at which Contains(target) was false */
+  uint32_t g_recovered;    /* first generation of the run of `stable_interval` matches */
+} lifeb200_hit;
+
+/* For each pattern p (device array `patterns`, n x 512 B) with target targets[target_index[p]]
+ * (targets: n_targets x {wanted[64], unwanted[64]} = 1024 B each, LifeTarget.hpp:5-7; a NULL
+ * target_index means target 0 for all): step up to `gens` generations evaluating Contains at every
+ * generation; a HIT is a pattern whose predicate was false at some generation >= 1 and later
+ * true for `stable_interval` consecutive generations.  Hits are compacted (warp ballot + one
+ * atomic per warp) into `hits` (device, capacity `cap`); *n_hits (device) receives the count.
+ * Patterns are not written back.  first_id is added to p in the reported id. */
+int lifeb200_step_match_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const uint64_t* targets,
+                            const uint32_t* target_index, size_t n, uint64_t first_id, unsigned gens,
+                            unsigned stable_interval, lifeb200_hit* hits, size_t cap,
+                            unsigned long long* n_hits);
+
+/* ---- A13 + A11  collision enumeration --------------------------
+ * Placement id = ((c * n_projectiles + g) * 64 + dx) * 64 + dy.  pattern = catalyst[c] |
+ * projectile[g].Moved(dx,dy) (LifeAPI.hpp:699-717, :247-253).  Placements whose ZOIs
+ * (LifeAPI.hpp:521-536) intersect at generation 0 are counted in *n_skipped and not stepped.
+ * Target of a placement = LifeTarget(catalyst[c]) (LifeTarget.hpp:10-13).  Everything is built on
+ * the device from the two small tables (HOST pointers: n_catalysts / n_projectiles x 512 B).
+ * Ids [id_begin, id_end) are processed (a rank's shard).  hits (HOST, capacity cap) come back
+ * sorted by id; returns LIFEB200_E_OVERFLOW with *n_hits = required if cap is too small. */
+int lifeb200_enumerate_collisions(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts,
+                                  const uint64_t* projectiles, unsigned n_projectiles, uint64_t id_begin,
+                                  uint64_t id_end, unsigned gens, unsigned stable_interval,
+                                  lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* n_skipped);
+
+/* ---- config 5  on-device soup survey ---------------------------------------------------
+ * Soups first_id..first_id+n-1 are generated in registers (never touch HBM), stepped `gens`
+ * generations (gens >= 2); a soup is ACTIVE iff state(gens) != state(gens-2)
+ * (operator== LifeAPI.hpp:213-220).  Active ids with their final population (GetPop,
+ * LifeAPI.hpp:290-298) are compacted into `hits` (HOST, sorted by id; hit.g_first_false = pop,
+ * hit.g_recovered = 0).  *pop_sum = sum of the final populations of ALL soups, *hash_xor = XOR of
+ * a 64-bit fold of every final state (checksum for size-independent parity). */
+int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t seed, int dist,
+                         unsigned gens, lifeb200_hit* hits, size_t cap, uint64_t* n_hits,
+                         uint64_t* pop_sum, uint64_t* hash_xor);
+/* The same 64-bit fold of a resident batch: XOR over patterns of fold(p). */
+int lifeb200_fold_dev(lifeb200_ctx* ctx, const uint64_t* patterns, size_t n, uint64_t first_id,
+                      uint64_t* pop_sum, uint64_t* hash_xor);
+
+/* ---- roofline denominator: measured LOP3 lane-instructions per second ------------------- */
+int lifeb200_measure_int_peak(lifeb200_ctx* ctx, double* lop3_lane_instr_per_s, double* sm_mhz_effective);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LIFEAPI_B200_H */

@@ -1,0 +1,297 @@
+"""ctypes binding of the C ABI in include/lifeapi_b200.h.
+
+This is the Python-side stub a maintainer would use to drive the library (INTEGRATION.md shows
+the C++ one).  It adds nothing: every method is one C call plus error translation.  There is no
+fallback of any kind -- if the shared library is missing, loading raises; if no sm_100 GPU is
+present, `Engine()` raises `LifeB200Error`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "_lib", "liblifeapi_b200.so")
+HEADER_PATH = os.path.join(HERE, "..", "include", "lifeapi_b200.h")
+
+WORDS = 64
+PATTERN_BYTES = 512
+
+E_OK, E_CUDA, E_ARG, E_OVERFLOW, E_NODEVICE = 0, 1, 2, 3, 4
+
+
+class LifeB200Error(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"lifeapi_b200 error {code}: {msg}")
+        self.code = code
+
+
+class Hit(C.Structure):
+    _fields_ = [("id", C.c_uint64), ("g_first_false", C.c_uint32), ("g_recovered", C.c_uint32)]
+
+
+HIT_DTYPE = np.dtype([("id", "<u8"), ("g_first_false", "<u4"), ("g_recovered", "<u4")])
+
+_u64p = C.POINTER(C.c_uint64)
+_vp = C.c_void_p
+
+# name -> (restype, argtypes); must list every function declared in the header
+SIGNATURES = {
+    "lifeb200_abi_version": (C.c_int, []),
+    "lifeb200_last_error": (C.c_char_p, []),
+    "lifeb200_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "lifeb200_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
+    "lifeb200_destroy": (C.c_int, [_vp]),
+    "lifeb200_set_stream": (C.c_int, [_vp, _vp]),
+    "lifeb200_sync": (C.c_int, [_vp]),
+    "lifeb200_device_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                       C.POINTER(C.c_int), C.POINTER(C.c_size_t)]),
+    "lifeb200_set_lanes_per_pattern": (C.c_int, [_vp, C.c_int]),
+    "lifeb200_malloc": (C.c_int, [_vp, C.POINTER(_vp), C.c_size_t]),
+    "lifeb200_free": (C.c_int, [_vp, _vp]),
+    "lifeb200_host_alloc": (C.c_int, [_vp, C.POINTER(_vp), C.c_size_t]),
+    "lifeb200_host_free": (C.c_int, [_vp, _vp]),
+    "lifeb200_memcpy_h2d": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_memcpy_d2h": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_memset": (C.c_int, [_vp, _vp, C.c_int, C.c_size_t]),
+    "lifeb200_timer_start": (C.c_int, [_vp]),
+    "lifeb200_timer_stop": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "lifeb200_launch_count": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "lifeb200_step_batch_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_uint]),
+    "lifeb200_step_batch_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_uint]),
+    "lifeb200_soup_dev": (C.c_int, [_vp, _vp, C.c_uint64, C.c_size_t, C.c_uint64, C.c_int]),
+    "lifeb200_neighbour_count_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_neighbour_count_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_step_match_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_uint64, C.c_uint, C.c_uint, _vp,
+                                          C.c_size_t, _vp]),
+    "lifeb200_enumerate_collisions": (C.c_int, [_vp, _vp, C.c_uint, _vp, C.c_uint, C.c_uint64, C.c_uint64, C.c_uint,
+                                                C.c_uint, _vp, C.c_size_t, _u64p, _u64p]),
+    "lifeb200_soup_survey": (C.c_int, [_vp, C.c_uint64, C.c_size_t, C.c_uint64, C.c_int, C.c_uint, _vp, C.c_size_t,
+                                       _u64p, _u64p, _u64p]),
+    "lifeb200_fold_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_uint64, _u64p, _u64p]),
+    "lifeb200_measure_int_peak": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+}
+
+
+def declared_functions(header_path: str = HEADER_PATH) -> list[str]:
+    """Names of every function the public header declares."""
+    text = open(header_path).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(lifeb200_[a-z0-9_]+)\s*\(", text)))
+
+
+_lib = None
+
+
+def load_library(path: str = LIB_PATH) -> C.CDLL:
+    """dlopen the in-tree library; raises OSError if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(path):
+            raise OSError(f"{path} not built: run `python -m lifeapi_b200.build` (needs nvcc)")
+        lib = C.CDLL(path)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def _ptr(a) -> int:
+    """Raw address of a numpy array, int (device pointer) or None."""
+    if a is None:
+        return 0
+    if isinstance(a, (int, np.integer)):
+        return int(a)
+    if isinstance(a, np.ndarray):
+        if not a.flags["C_CONTIGUOUS"]:
+            raise ValueError("array must be C-contiguous")
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):  # torch tensor (device or host)
+        return int(a.data_ptr())
+    raise TypeError(type(a))
+
+
+class Engine:
+    """One context == one GPU + one stream (lifeb200_create)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        h = _vp()
+        self._h = None
+        self._check(self.lib.lifeb200_create(device, C.byref(h)))
+        self._h = h
+        self.device = device
+
+    def _check(self, rc: int) -> None:
+        if rc != 0:
+            raise LifeB200Error(rc, self.lib.lifeb200_last_error().decode())
+
+    def close(self) -> None:
+        if self._h is not None:
+            self.lib.lifeb200_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- management --------------------------------------------------------------------------
+    def set_stream(self, cuda_stream: int | None) -> None:
+        self._check(self.lib.lifeb200_set_stream(self._h, cuda_stream or None))
+
+    def sync(self) -> None:
+        self._check(self.lib.lifeb200_sync(self._h))
+
+    def set_lanes_per_pattern(self, lpp: int) -> None:
+        self._check(self.lib.lifeb200_set_lanes_per_pattern(self._h, lpp))
+
+    def device_info(self) -> dict:
+        sm, ma, mi, khz, mem = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_size_t()
+        self._check(self.lib.lifeb200_device_info(self._h, C.byref(sm), C.byref(ma), C.byref(mi), C.byref(khz), C.byref(mem)))
+        return {"sm_count": sm.value, "cc": (ma.value, mi.value), "clock_khz": khz.value, "total_mem": mem.value}
+
+    def launch_count(self) -> int:
+        v = C.c_uint64()
+        self._check(self.lib.lifeb200_launch_count(self._h, C.byref(v)))
+        return v.value
+
+    def timer_start(self) -> None:
+        self._check(self.lib.lifeb200_timer_start(self._h))
+
+    def timer_stop(self) -> float:
+        ms = C.c_float()
+        self._check(self.lib.lifeb200_timer_stop(self._h, C.byref(ms)))
+        return ms.value
+
+    def measure_int_peak(self) -> tuple[float, float]:
+        r, mhz = C.c_double(), C.c_double()
+        self._check(self.lib.lifeb200_measure_int_peak(self._h, C.byref(r), C.byref(mhz)))
+        return r.value, mhz.value
+
+    # -- memory ------------------------------------------------------------------------------
+    def malloc(self, nbytes: int) -> int:
+        p = _vp()
+        self._check(self.lib.lifeb200_malloc(self._h, C.byref(p), nbytes))
+        return p.value or 0
+
+    def free(self, dptr: int) -> None:
+        self._check(self.lib.lifeb200_free(self._h, dptr))
+
+    def host_alloc(self, shape, dtype=np.uint64) -> np.ndarray:
+        """Pinned host array (lifeb200_host_alloc); freed with host_free(arr)."""
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape)) * dtype.itemsize
+        p = _vp()
+        self._check(self.lib.lifeb200_host_alloc(self._h, C.byref(p), max(n, 1)))
+        buf = (C.c_char * max(n, 1)).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+        arr.flags.writeable = True
+        return arr
+
+    def host_free(self, arr: np.ndarray) -> None:
+        self._check(self.lib.lifeb200_host_free(self._h, arr.ctypes.data))
+
+    def h2d(self, dptr: int, src: np.ndarray) -> None:
+        self._check(self.lib.lifeb200_memcpy_h2d(self._h, dptr, _ptr(src), src.nbytes))
+
+    def d2h(self, dst: np.ndarray, dptr: int) -> None:
+        self._check(self.lib.lifeb200_memcpy_d2h(self._h, _ptr(dst), dptr, dst.nbytes))
+
+    def memset(self, dptr: int, value: int, nbytes: int) -> None:
+        self._check(self.lib.lifeb200_memset(self._h, dptr, value, nbytes))
+
+    # -- compute -----------------------------------------------------------------------------
+    def step_batch_dev(self, d_in, d_out, n: int, gens: int) -> None:
+        self._check(self.lib.lifeb200_step_batch_dev(self._h, _ptr(d_in), _ptr(d_out), n, gens))
+
+    def step_batch_host(self, src: np.ndarray, gens: int, out: np.ndarray | None = None) -> np.ndarray:
+        src = np.ascontiguousarray(src, dtype=np.uint64)
+        n = src.size // WORDS
+        if out is None:
+            out = np.empty_like(src)
+        self._check(self.lib.lifeb200_step_batch_host(self._h, _ptr(src), _ptr(out), n, gens))
+        return out
+
+    def soup_dev(self, d_out, first_id: int, n: int, seed: int, dist: int = 0) -> None:
+        self._check(self.lib.lifeb200_soup_dev(self._h, _ptr(d_out), first_id, n, seed, dist))
+
+    def neighbour_count_dev(self, d_in, d_planes, n: int) -> None:
+        self._check(self.lib.lifeb200_neighbour_count_dev(self._h, _ptr(d_in), _ptr(d_planes), n))
+
+    def neighbour_count_host(self, src: np.ndarray) -> np.ndarray:
+        src = np.ascontiguousarray(src, dtype=np.uint64)
+        n = src.size // WORDS
+        out = np.empty((n, 4, WORDS), dtype=np.uint64)
+        self._check(self.lib.lifeb200_neighbour_count_host(self._h, _ptr(src), _ptr(out), n))
+        return out
+
+    def step_match_dev(self, d_patterns, d_targets, d_target_index, n, first_id, gens, stable_interval, d_hits, cap,
+                       d_n_hits) -> None:
+        self._check(self.lib.lifeb200_step_match_dev(self._h, _ptr(d_patterns), _ptr(d_targets), _ptr(d_target_index), n,
+                                                     first_id, gens, stable_interval, _ptr(d_hits), cap, _ptr(d_n_hits)))
+
+    def step_match(self, patterns: np.ndarray, targets: np.ndarray, target_index: np.ndarray | None, gens: int,
+                   stable_interval: int, first_id: int = 0, cap: int | None = None) -> np.ndarray:
+        """Convenience: host arrays in, sorted hit records out (uses only *_dev entry points)."""
+        patterns = np.ascontiguousarray(patterns, dtype=np.uint64)
+        targets = np.ascontiguousarray(targets, dtype=np.uint64)
+        n = patterns.size // WORDS
+        cap = n if cap is None else cap
+        d_p = self.malloc(max(patterns.nbytes, 16))
+        d_t = self.malloc(max(targets.nbytes, 16))
+        d_i = 0
+        d_h = self.malloc(max(cap, 1) * 16)
+        d_n = self.malloc(8)
+        try:
+            self.h2d(d_p, patterns)
+            self.h2d(d_t, targets)
+            if target_index is not None:
+                target_index = np.ascontiguousarray(target_index, dtype=np.uint32)
+                d_i = self.malloc(max(target_index.nbytes, 16))
+                self.h2d(d_i, target_index)
+            self.step_match_dev(d_p, d_t, d_i or None, n, first_id, gens, stable_interval, d_h, cap, d_n)
+            cnt = np.zeros(1, dtype=np.uint64)
+            self.d2h(cnt, d_n)
+            self.sync()
+            found = int(cnt[0])
+            if found > cap:
+                raise LifeB200Error(E_OVERFLOW, f"{found} hits, capacity {cap}")
+            hits = np.zeros(found, dtype=HIT_DTYPE)
+            if found:
+                self.d2h(hits, d_h)
+                self.sync()
+            return np.sort(hits, order="id")
+        finally:
+            for p in (d_p, d_t, d_i, d_h, d_n):
+                if p:
+                    self.free(p)
+
+    def enumerate_collisions(self, catalysts: np.ndarray, projectiles: np.ndarray, id_begin: int, id_end: int, gens: int,
+                             stable_interval: int, cap: int) -> tuple[np.ndarray, int]:
+        catalysts = np.ascontiguousarray(catalysts, dtype=np.uint64)
+        projectiles = np.ascontiguousarray(projectiles, dtype=np.uint64)
+        hits = np.zeros(max(cap, 1), dtype=HIT_DTYPE)
+        nh, ns = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.lifeb200_enumerate_collisions(
+            self._h, _ptr(catalysts), catalysts.size // WORDS, _ptr(projectiles), projectiles.size // WORDS, id_begin,
+            id_end, gens, stable_interval, _ptr(hits), cap, C.byref(nh), C.byref(ns)))
+        return hits[: nh.value].copy(), ns.value
+
+    def soup_survey(self, first_id: int, n: int, seed: int, dist: int, gens: int, cap: int):
+        hits = np.zeros(max(cap, 1), dtype=HIT_DTYPE)
+        nh, ps, hx = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._check(self.lib.lifeb200_soup_survey(self._h, first_id, n, seed, dist, gens, _ptr(hits), cap, C.byref(nh),
+                                                  C.byref(ps), C.byref(hx)))
+        return hits[: nh.value].copy(), ps.value, hx.value
+
+    def fold_dev(self, d_patterns, n: int, first_id: int = 0) -> tuple[int, int]:
+        ps, hx = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.lifeb200_fold_dev(self._h, _ptr(d_patterns), n, first_id, C.byref(ps), C.byref(hx)))
+        return ps.value, hx.value

@@ -1,0 +1,81 @@
+// ctx.h -- internal: context object, error plumbing and launch helpers shared by the .cu files.
+#pragma once
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cuda_runtime.h>
+
+#include "../../include/lifeapi_b200.h"
+
+namespace lifeb200 {
+
+constexpr int kSlots = 3;  // host-path pipeline depth (H2D | kernel | D2H in flight)
+
+struct Slot {
+  cudaStream_t stream = nullptr;
+  void* dbuf = nullptr;   // device staging
+  void* dbuf2 = nullptr;  // second device staging (outputs larger than inputs)
+  size_t cap = 0, cap2 = 0;
+};
+
+}  // namespace lifeb200
+
+struct lifeb200_ctx {
+  int device = 0;
+  int sm_count = 0;
+  int cc_major = 0, cc_minor = 0;
+  int clock_khz = 0;
+  size_t total_mem = 0;
+  int lpp = 0;  // 0 = default
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;  // == own_stream unless lifeb200_set_stream
+  cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+  uint64_t launches = 0;
+  lifeb200::Slot slots[lifeb200::kSlots];
+  // small device scratch for counters: [0]=n_hits [1]=n_skipped [2]=pop_sum [3]=hash_xor
+  unsigned long long* d_counters = nullptr;
+  unsigned long long* h_counters = nullptr;  // pinned mirror
+};
+
+namespace lifeb200 {
+
+int set_error(int code, const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+int ensure_slot(lifeb200_ctx* ctx, int slot, size_t bytes, size_t bytes2);
+
+#define LIFEB200_CUDA(expr)                                                        \
+  do {                                                                             \
+    cudaError_t _e = (expr);                                                       \
+    if (_e != cudaSuccess) return lifeb200::cuda_fail(_e, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+#define LIFEB200_CHECK_CTX(ctx)                                              \
+  do {                                                                       \
+    if (!(ctx)) return lifeb200::set_error(LIFEB200_E_ARG, "null context"); \
+    LIFEB200_CUDA(cudaSetDevice((ctx)->device));                             \
+  } while (0)
+
+#define LIFEB200_LAUNCHED(ctx)       \
+  do {                               \
+    (ctx)->launches++;               \
+    LIFEB200_CUDA(cudaGetLastError()); \
+  } while (0)
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+constexpr int kDefaultLpp = 8;
+inline int effective_lpp(const lifeb200_ctx* ctx) { return ctx->lpp ? ctx->lpp : kDefaultLpp; }
+
+// dispatch a functor templated on lanes-per-pattern
+#define LIFEB200_DISPATCH_LPP(lpp, CALL) \
+  switch (lpp) {                         \
+    case 1: { constexpr int LPP = 1; CALL; } break;   \
+    case 2: { constexpr int LPP = 2; CALL; } break;   \
+    case 4: { constexpr int LPP = 4; CALL; } break;   \
+    case 8: { constexpr int LPP = 8; CALL; } break;   \
+    case 16: { constexpr int LPP = 16; CALL; } break; \
+    case 32: { constexpr int LPP = 32; CALL; } break; \
+    default: return lifeb200::set_error(LIFEB200_E_ARG, "lanes per pattern must be 1,2,4,8,16,32"); \
+  }
+
+}  // namespace lifeb200

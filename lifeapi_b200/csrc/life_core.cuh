@@ -1,0 +1,218 @@
+// life_core.cuh -- register-resident 64x64 torus tile and the B3/S23 generation step (sm_100a).
+//
+// Layout is the reference's (LifeAPI.hpp:39-40,131): a pattern is uint64_t state[64]; word index
+// = column x, bit index = row y.  A pattern is owned by LPP consecutive lanes of one warp
+// ("lanes per pattern"); each lane keeps W = 64/LPP consecutive words as (lo,hi) 32-bit register
+// pairs.  Bit neighbours (y+-1) come from 64-bit rotates built from SHF funnel shifts; word
+// neighbours (x+-1) are the adjacent registers, and at the lane boundary the 2-bit column counts
+// are exchanged with __shfl_sync whose width=LPP argument gives the torus wrap.
+//
+// The rule is LifeState::StepAlt (LifeAPI.hpp:1218-1254) restated as 3-input LUTs:
+//   per 32-cell half-word and generation: 2 SHF + 10 LOP3.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace lifeb200 {
+
+constexpr int kN = 64;  // LifeAPI.hpp:12
+
+template <int LUT>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(d) : "r"(a), "r"(b), "r"(c), "n"(LUT));
+  return d;
+}
+// truth tables with a=0xF0, b=0xCC, c=0xAA
+constexpr int kXor3 = 0x96;       // a^b^c
+constexpr int kMaj = 0xE8;        // (a&b)|(c&(a^b))
+constexpr int kXorAnd = 0x78;     // a^(b&c)
+constexpr int kXorThenAnd = 0x28; // (a^b)&c
+constexpr int kAndOr = 0xE0;      // a&(b|c)
+constexpr int kOr3 = 0xFE;        // a|b|c
+constexpr int kAndXor = 0x6A;     // (a&b)^c
+constexpr int kOrAnd = 0xEA;      // (a&b)|c
+
+// 2-bit count of the (y-1, y, y+1) triple inside one column word: LifeAPI.hpp:897-907 CountRows.
+struct Cnt {
+  uint32_t b0lo, b0hi, b1lo, b1hi;
+};
+
+__device__ __forceinline__ Cnt count_rows(uint32_t lo, uint32_t hi) {
+  // rotl64(a,1) / rotr64(a,1) on the (lo,hi) pair: 4 SHF
+  uint32_t l_lo = __funnelshift_l(hi, lo, 1), l_hi = __funnelshift_l(lo, hi, 1);
+  uint32_t r_lo = __funnelshift_r(lo, hi, 1), r_hi = __funnelshift_r(hi, lo, 1);
+  Cnt c;
+  c.b0lo = lop3<kXor3>(l_lo, r_lo, lo);
+  c.b0hi = lop3<kXor3>(l_hi, r_hi, hi);
+  c.b1lo = lop3<kMaj>(l_lo, r_lo, lo);
+  c.b1hi = lop3<kMaj>(l_hi, r_hi, hi);
+  return c;
+}
+
+// StepAlt tail (LifeAPI.hpp:1236-1252): two full adders over the three column counts, carry
+// fix-up and the B3/S23 select.  8 LOP3 per half-word.
+__device__ __forceinline__ uint32_t rule32(uint32_t a, uint32_t u0, uint32_t u1, uint32_t c0, uint32_t c1,
+                                           uint32_t d0, uint32_t d1) {
+  uint32_t fs = lop3<kXor3>(u0, c0, d0);
+  uint32_t fc = lop3<kMaj>(u0, c0, d0);
+  uint32_t cs = lop3<kXor3>(u1, c1, d1);
+  uint32_t cc = lop3<kMaj>(u1, c1, d1);
+  cc = lop3<kXorAnd>(cc, fc, cs);
+  uint32_t y = lop3<kXor3>(fc, cs, cc);
+  uint32_t t = lop3<kXorThenAnd>(fs, cc, y);
+  return lop3<kAndOr>(t, a, fs);
+}
+
+template <int LPP>
+__device__ __forceinline__ Cnt halo(const Cnt& c, int src) {
+  if constexpr (LPP == 1) {
+    return c;
+  } else {
+    Cnt r;
+    r.b0lo = __shfl_sync(0xffffffffu, c.b0lo, src, LPP);
+    r.b0hi = __shfl_sync(0xffffffffu, c.b0hi, src, LPP);
+    r.b1lo = __shfl_sync(0xffffffffu, c.b1lo, src, LPP);
+    r.b1hi = __shfl_sync(0xffffffffu, c.b1hi, src, LPP);
+    return r;
+  }
+}
+
+// One pattern slice held by one lane.
+template <int LPP>
+struct Tile {
+  static constexpr int W = kN / LPP;
+  static_assert(LPP == 1 || LPP == 2 || LPP == 4 || LPP == 8 || LPP == 16 || LPP == 32, "LPP");
+  uint32_t lo[W], hi[W];
+
+  // sub = lane index inside the pattern's lane group (0..LPP-1)
+  __device__ __forceinline__ void load(const uint64_t* __restrict__ pat, int sub) {
+    const uint4* p = reinterpret_cast<const uint4*>(pat + sub * W);
+#pragma unroll
+    for (int k = 0; k < W / 2; k++) {
+      uint4 v = __ldg(p + k);
+      lo[2 * k] = v.x; hi[2 * k] = v.y; lo[2 * k + 1] = v.z; hi[2 * k + 1] = v.w;
+    }
+  }
+  __device__ __forceinline__ void store(uint64_t* __restrict__ pat, int sub) const {
+    uint4* p = reinterpret_cast<uint4*>(pat + sub * W);
+#pragma unroll
+    for (int k = 0; k < W / 2; k++) p[k] = make_uint4(lo[2 * k], hi[2 * k], lo[2 * k + 1], hi[2 * k + 1]);
+  }
+
+  // One generation in place == LifeState::Step() (LifeAPI.hpp:1196-1216), rolling 3-column window.
+  __device__ __forceinline__ void step(int sub) {
+    const int up_src = sub + LPP - 1, dn_src = sub + 1;  // taken modulo LPP by shfl width
+    Cnt first = count_rows(lo[0], hi[0]);
+    Cnt last = (W == 1) ? first : count_rows(lo[W - 1], hi[W - 1]);
+    Cnt prev = halo<LPP>(last, up_src);
+    Cnt after = halo<LPP>(first, dn_src);
+    Cnt cur = first;
+#pragma unroll
+    for (int w = 0; w < W; w++) {
+      Cnt next;
+      if (w == W - 1) next = after;
+      else if (w + 1 == W - 1) next = last;
+      else next = count_rows(lo[w + 1], hi[w + 1]);
+      uint32_t nlo = rule32(lo[w], prev.b0lo, prev.b1lo, cur.b0lo, cur.b1lo, next.b0lo, next.b1lo);
+      uint32_t nhi = rule32(hi[w], prev.b0hi, prev.b1hi, cur.b0hi, cur.b1hi, next.b0hi, next.b1hi);
+      lo[w] = nlo; hi[w] = nhi;
+      prev = cur; cur = next;
+    }
+  }
+
+  // NeighbourCount(const LifeState&) (NeighbourCount.hpp:40-70 == LifeAPI.hpp:909-952): the four
+  // bit planes of the 3x3 sum INCLUDING the centre (0..9).  The planes are the binary digits of a
+  // sum, so any exact adder gives the reference's bits: two 3:2 compressors over the column
+  // counts, then total = s0 + 2(k0 + s1) + 4 k1.
+  __device__ __forceinline__ void neighbour_count(int sub, Tile& b3, Tile& b2, Tile& b1, Tile& b0) const {
+    const int up_src = sub + LPP - 1, dn_src = sub + 1;
+    Cnt first = count_rows(lo[0], hi[0]);
+    Cnt last = (W == 1) ? first : count_rows(lo[W - 1], hi[W - 1]);
+    Cnt prev = halo<LPP>(last, up_src);
+    Cnt after = halo<LPP>(first, dn_src);
+    Cnt cur = first;
+#pragma unroll
+    for (int w = 0; w < W; w++) {
+      Cnt next;
+      if (w == W - 1) next = after;
+      else if (w + 1 == W - 1) next = last;
+      else next = count_rows(lo[w + 1], hi[w + 1]);
+      {
+        uint32_t s0 = lop3<kXor3>(prev.b0lo, cur.b0lo, next.b0lo), k0 = lop3<kMaj>(prev.b0lo, cur.b0lo, next.b0lo);
+        uint32_t s1 = lop3<kXor3>(prev.b1lo, cur.b1lo, next.b1lo), k1 = lop3<kMaj>(prev.b1lo, cur.b1lo, next.b1lo);
+        uint32_t cy = k0 & s1;
+        b0.lo[w] = s0; b1.lo[w] = k0 ^ s1; b2.lo[w] = k1 ^ cy; b3.lo[w] = k1 & cy;
+      }
+      {
+        uint32_t s0 = lop3<kXor3>(prev.b0hi, cur.b0hi, next.b0hi), k0 = lop3<kMaj>(prev.b0hi, cur.b0hi, next.b0hi);
+        uint32_t s1 = lop3<kXor3>(prev.b1hi, cur.b1hi, next.b1hi), k1 = lop3<kMaj>(prev.b1hi, cur.b1hi, next.b1hi);
+        uint32_t cy = k0 & s1;
+        b0.hi[w] = s0; b1.hi[w] = k0 ^ s1; b2.hi[w] = k1 ^ cy; b3.hi[w] = k1 & cy;
+      }
+      prev = cur; cur = next;
+    }
+  }
+
+  // OR over this lane's words of (state ^ wanted) & (wanted | unwanted): LifeTarget.hpp:44-51.
+  // wm = wanted & mask, m = wanted | unwanted (precomputed per target).
+  __device__ __forceinline__ uint32_t target_diff(const Tile& wm, const Tile& m) const {
+    uint32_t d = 0;
+#pragma unroll
+    for (int w = 0; w < W; w++) {
+      uint32_t t0 = lop3<kAndXor>(lo[w], m.lo[w], wm.lo[w]);
+      uint32_t t1 = lop3<kAndXor>(hi[w], m.hi[w], wm.hi[w]);
+      d = lop3<kOr3>(d, t0, t1);
+    }
+    return d;
+  }
+  __device__ __forceinline__ uint32_t xor_diff(const Tile& o) const {  // operator== LifeAPI.hpp:213-220
+    uint32_t d = 0;
+#pragma unroll
+    for (int w = 0; w < W; w++) d |= (lo[w] ^ o.lo[w]) | (hi[w] ^ o.hi[w]);
+    return d;
+  }
+  __device__ __forceinline__ uint32_t any_bits() const {  // IsEmpty LifeAPI.hpp:281-288
+    uint32_t d = 0;
+#pragma unroll
+    for (int w = 0; w < W; w++) d = lop3<kOr3>(d, lo[w], hi[w]);
+    return d;
+  }
+  __device__ __forceinline__ uint32_t pop() const {  // GetPop LifeAPI.hpp:290-298 (this lane's share)
+    uint32_t p = 0;
+#pragma unroll
+    for (int w = 0; w < W; w++) p += __popc(lo[w]) + __popc(hi[w]);
+    return p;
+  }
+};
+
+// group-wide reductions over the LPP lanes owning one pattern
+template <int LPP>
+__device__ __forceinline__ bool group_any(bool pred, int lane) {
+  if constexpr (LPP == 1) return pred;
+  unsigned b = __ballot_sync(0xffffffffu, pred);
+  if constexpr (LPP == 32) return b != 0;
+  unsigned gmask = ((1u << (LPP & 31)) - 1u) << (lane & ~(LPP - 1));
+  return (b & gmask) != 0;
+}
+template <int LPP>
+__device__ __forceinline__ uint32_t group_sum(uint32_t v) {
+#pragma unroll
+  for (int o = LPP / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o, 32);
+  return v;
+}
+
+// splitmix64 soup source (build-defined; replaces LifeAPI.hpp:63-69).
+__device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
+  z += 0x9E3779B97F4A7C15ULL;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  return z ^ (z >> 31);
+}
+__device__ __forceinline__ uint64_t soup_word(uint64_t seed, uint64_t id, int i, int dist) {
+  uint64_t r = splitmix64(seed + id * 64 + (uint64_t)i);
+  if (dist == 1) r = (1ULL << 61) + (r % ((1ULL << 61) + 1));  // shape of LifeAPI.hpp:21-22
+  return r;
+}
+
+}  // namespace lifeb200

@@ -1,0 +1,390 @@
+// match.cu -- stepping fused with LifeState::Contains(const LifeTarget&) (LifeTarget.hpp:44-51),
+// placement construction (Moved/operator|, LifeAPI.hpp:699-717,247-253), the soup survey with the
+// period-2 activity test (operator==, LifeAPI.hpp:213-220) and hit compaction.
+#include <algorithm>
+#include <vector>
+
+#include "ctx.h"
+#include "life_core.cuh"
+
+namespace lifeb200 {
+
+constexpr int kBlockM = 256;
+
+// Per-pattern recovery state machine, identical in every lane of the pattern's group.
+struct Recovery {
+  unsigned first_false = 0, run = 0, recovered = 0;
+  bool seen_false = false, hit = false, done = false;
+  __device__ __forceinline__ void observe(bool mismatch, unsigned g, unsigned stable_interval) {
+    if (done) return;
+    if (mismatch) {
+      if (!seen_false) { seen_false = true; first_false = g; }
+      run = 0;
+    } else if (seen_false) {
+      if (++run == stable_interval) { hit = true; done = true; recovered = g + 1 - stable_interval; }
+    }
+  }
+};
+
+// Warp-aggregated append: one atomicAdd per warp, hits beyond `cap` are counted but not written.
+__device__ __forceinline__ void append_hit(bool emit, uint64_t id, uint32_t a, uint32_t b, lifeb200_hit* hits,
+                                           size_t cap, unsigned long long* n_hits) {
+  unsigned m = __ballot_sync(0xffffffffu, emit);
+  if (m == 0) return;
+  int lane = threadIdx.x & 31;
+  int leader = __ffs(m) - 1;
+  unsigned long long base = 0;
+  if (lane == leader) base = atomicAdd(n_hits, (unsigned long long)__popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (emit) {
+    unsigned long long slot = base + __popc(m & ((1u << lane) - 1u));
+    if (slot < cap) {
+      lifeb200_hit h;
+      h.id = id; h.g_first_false = a; h.g_recovered = b;
+      hits[slot] = h;
+    }
+  }
+}
+
+template <int LPP>
+__device__ __forceinline__ void run_match(Tile<LPP>& t, const Tile<LPP>& wm, const Tile<LPP>& m, int sub, int lane,
+                                          unsigned gens, unsigned stable_interval, Recovery& r) {
+#pragma unroll 1
+  for (unsigned g = 1; g <= gens; g++) {
+    t.step(sub);
+    uint32_t d = t.target_diff(wm, m);
+    bool mismatch = group_any<LPP>(d != 0, lane);
+    r.observe(mismatch, g, stable_interval);
+    if ((g & 7u) == 0 && __all_sync(0xffffffffu, r.done)) break;
+  }
+}
+
+template <int LPP>
+__global__ void __launch_bounds__(kBlockM) step_match_kernel(const uint64_t* __restrict__ patterns,
+                                                             const uint64_t* __restrict__ targets,
+                                                             const uint32_t* __restrict__ target_index, size_t n,
+                                                             uint64_t first_id, unsigned gens, unsigned stable_interval,
+                                                             lifeb200_hit* hits, size_t cap, unsigned long long* n_hits) {
+  constexpr int W = Tile<LPP>::W;
+  const size_t gid = (size_t)blockIdx.x * kBlockM + threadIdx.x;
+  const size_t p = gid / LPP;
+  const int lane = threadIdx.x & 31, sub = threadIdx.x & (LPP - 1);
+  const bool valid = p < n;
+  Tile<LPP> t, wm, m;
+  Recovery r;
+  if (valid) {
+    t.load(patterns + p * kN, sub);
+    const uint64_t* tg = targets + (size_t)(target_index ? target_index[p] : 0u) * 2 * kN;
+    wm.load(tg, sub);       // wanted
+    m.load(tg + kN, sub);   // unwanted
+#pragma unroll
+    for (int w = 0; w < W; w++) {
+      m.lo[w] |= wm.lo[w]; m.hi[w] |= wm.hi[w];  // mask = wanted | unwanted
+    }
+  } else {
+#pragma unroll
+    for (int w = 0; w < W; w++) t.lo[w] = t.hi[w] = wm.lo[w] = wm.hi[w] = m.lo[w] = m.hi[w] = 0;
+    r.done = true;
+  }
+  run_match<LPP>(t, wm, m, sub, lane, gens, stable_interval, r);
+  append_hit(valid && r.hit && sub == 0, first_id + p, r.first_false, r.recovered, hits, cap, n_hits);
+}
+
+__device__ __forceinline__ uint64_t rotl64v(uint64_t v, unsigned s) {
+  s &= 63u;
+  return s ? (v << s) | (v >> (64u - s)) : v;
+}
+
+// tables: [cat | catZOI | proj | projZOI], each entry 64 words.
+template <int LPP>
+__global__ void __launch_bounds__(kBlockM) enumerate_kernel(const uint64_t* __restrict__ cat,
+                                                            const uint64_t* __restrict__ cat_zoi,
+                                                            const uint64_t* __restrict__ proj,
+                                                            const uint64_t* __restrict__ proj_zoi, unsigned n_proj,
+                                                            uint64_t id_begin, uint64_t id_end, unsigned gens,
+                                                            unsigned stable_interval, lifeb200_hit* hits, size_t cap,
+                                                            unsigned long long* n_hits, unsigned long long* n_skipped) {
+  constexpr int W = Tile<LPP>::W;
+  const uint64_t gid = (uint64_t)blockIdx.x * kBlockM + threadIdx.x;
+  const uint64_t id = id_begin + gid / LPP;
+  const int lane = threadIdx.x & 31, sub = threadIdx.x & (LPP - 1);
+  const bool valid = id < id_end;
+  Tile<LPP> t, wm, m;
+  Recovery r;
+  uint32_t overlap = 0;
+  if (valid) {
+    const unsigned dy = (unsigned)(id & 63u), dx = (unsigned)((id >> 6) & 63u);
+    const uint64_t cg = id >> 12;
+    const unsigned g = (unsigned)(cg % n_proj);
+    const uint64_t c = cg / n_proj;
+    const uint64_t* cw = cat + c * kN;
+    const uint64_t* cz = cat_zoi + c * kN;
+    const uint64_t* pw = proj + (size_t)g * kN;
+    const uint64_t* pz = proj_zoi + (size_t)g * kN;
+#pragma unroll
+    for (int w = 0; w < W; w++) {
+      const int i = sub * W + w;
+      const int src = (i - (int)dx) & 63;  // Moved: result[i] = rotl(state[i - x], y)
+      uint64_t cat_w = __ldg(cw + i), zoi_w = __ldg(cz + i);
+      uint64_t pm = rotl64v(__ldg(pw + src), dy), pzm = rotl64v(__ldg(pz + src), dy);
+      uint64_t s = cat_w | pm;
+      t.lo[w] = (uint32_t)s; t.hi[w] = (uint32_t)(s >> 32);
+      // LifeTarget(catalyst): wanted = cat, unwanted = ZOI & ~cat  =>  mask = ZOI, wanted&mask = cat
+      wm.lo[w] = (uint32_t)cat_w; wm.hi[w] = (uint32_t)(cat_w >> 32);
+      m.lo[w] = (uint32_t)zoi_w; m.hi[w] = (uint32_t)(zoi_w >> 32);
+      uint64_t ov = zoi_w & pzm;
+      overlap |= (uint32_t)ov | (uint32_t)(ov >> 32);
+    }
+  } else {
+#pragma unroll
+    for (int w = 0; w < W; w++) t.lo[w] = t.hi[w] = wm.lo[w] = wm.hi[w] = m.lo[w] = m.hi[w] = 0;
+  }
+  const bool skip = group_any<LPP>(overlap != 0, lane);
+  if (!valid || skip) r.done = true;
+  {
+    unsigned sk = __ballot_sync(0xffffffffu, valid && skip && sub == 0);
+    if (lane == 0 && sk) atomicAdd(n_skipped, (unsigned long long)__popc(sk));
+  }
+  run_match<LPP>(t, wm, m, sub, lane, gens, stable_interval, r);
+  append_hit(valid && r.hit && sub == 0, id, r.first_false, r.recovered, hits, cap, n_hits);
+}
+
+// Per-pattern 64-bit fold used as a size-independent checksum (build-defined):
+// fold(p) = XOR_i splitmix64(state[i] + i*K);  batch = XOR_p splitmix64(fold(p) + id_p).
+constexpr uint64_t kFoldK = 0xD6E8FEB86659FD93ULL;
+template <int LPP>
+__device__ __forceinline__ uint64_t group_fold(const Tile<LPP>& t, int sub) {
+  constexpr int W = Tile<LPP>::W;
+  uint64_t f = 0;
+#pragma unroll
+  for (int w = 0; w < W; w++) {
+    uint64_t v = ((uint64_t)t.hi[w] << 32) | t.lo[w];
+    f ^= splitmix64(v + (uint64_t)(sub * W + w) * kFoldK);
+  }
+#pragma unroll
+  for (int o = LPP / 2; o > 0; o >>= 1) f ^= __shfl_xor_sync(0xffffffffu, f, o, 32);
+  return f;
+}
+
+__device__ __forceinline__ void block_accumulate(uint64_t pop, uint64_t h, unsigned long long* pop_sum,
+                                                 unsigned long long* hash_xor) {
+  // warp reduce, then one atomic pair per warp
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    pop += __shfl_xor_sync(0xffffffffu, pop, o, 32);
+    h ^= __shfl_xor_sync(0xffffffffu, h, o, 32);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(pop_sum, (unsigned long long)pop);
+    atomicXor(hash_xor, (unsigned long long)h);
+  }
+}
+
+template <int LPP>
+__global__ void __launch_bounds__(kBlockM) survey_kernel(uint64_t first_id, size_t n, uint64_t seed, int dist,
+                                                         unsigned gens, lifeb200_hit* hits, size_t cap,
+                                                         unsigned long long* n_hits, unsigned long long* pop_sum,
+                                                         unsigned long long* hash_xor) {
+  constexpr int W = Tile<LPP>::W;
+  const size_t gid = (size_t)blockIdx.x * kBlockM + threadIdx.x;
+  const size_t p = gid / LPP;
+  const int lane = threadIdx.x & 31, sub = threadIdx.x & (LPP - 1);
+  const bool valid = p < n;
+  const uint64_t id = first_id + p;
+  Tile<LPP> t, before;
+#pragma unroll
+  for (int w = 0; w < W; w++) {
+    uint64_t v = valid ? soup_word(seed, id, sub * W + w, dist) : 0ULL;
+    t.lo[w] = (uint32_t)v; t.hi[w] = (uint32_t)(v >> 32);
+  }
+#pragma unroll 1
+  for (unsigned g = 0; g + 2 < gens; g++) t.step(sub);
+  before = t;
+  t.step(sub);
+  t.step(sub);
+  const bool active = group_any<LPP>(t.xor_diff(before) != 0, lane);
+  const uint32_t pop = group_sum<LPP>(t.pop());
+  const uint64_t f = group_fold<LPP>(t, sub);
+  const bool leader = valid && sub == 0;
+  block_accumulate(leader ? pop : 0u, leader ? splitmix64(f + id) : 0ULL, pop_sum, hash_xor);
+  append_hit(leader && active, id, pop, 0u, hits, cap, n_hits);
+}
+
+template <int LPP>
+__global__ void __launch_bounds__(kBlockM) fold_kernel(const uint64_t* __restrict__ patterns, size_t n, uint64_t first_id,
+                                                       unsigned long long* pop_sum, unsigned long long* hash_xor) {
+  constexpr int W = Tile<LPP>::W;
+  const size_t gid = (size_t)blockIdx.x * kBlockM + threadIdx.x;
+  const size_t p = gid / LPP;
+  const int sub = threadIdx.x & (LPP - 1);
+  const bool valid = p < n;
+  Tile<LPP> t;
+  if (valid) t.load(patterns + p * kN, sub);
+  else {
+#pragma unroll
+    for (int w = 0; w < W; w++) t.lo[w] = t.hi[w] = 0;
+  }
+  const uint32_t pop = group_sum<LPP>(t.pop());
+  const uint64_t f = group_fold<LPP>(t, sub);
+  const bool leader = valid && sub == 0;
+  block_accumulate(leader ? pop : 0u, leader ? splitmix64(f + first_id + p) : 0ULL, pop_sum, hash_xor);
+}
+
+static inline unsigned grid_m(uint64_t n, int lpp) { return (unsigned)((n * (uint64_t)lpp + kBlockM - 1) / kBlockM); }
+
+static void host_zoi(const uint64_t* s, uint64_t* out) {  // LifeAPI.hpp:521-536
+  uint64_t t[64];
+  for (int i = 0; i < 64; i++) t[i] = s[i] | (s[i] << 1 | s[i] >> 63) | (s[i] >> 1 | s[i] << 63);
+  for (int i = 0; i < 64; i++) out[i] = t[(i + 63) & 63] | t[i] | t[(i + 1) & 63];
+}
+
+// match kernels keep three tiles (state, wanted&mask, mask) in registers: cap W at 16.
+static inline int match_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
+static inline int survey_lpp(const lifeb200_ctx* ctx) { return std::max(2, effective_lpp(ctx)); }
+
+}  // namespace lifeb200
+
+using namespace lifeb200;
+
+extern "C" {
+
+int lifeb200_step_match_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const uint64_t* targets,
+                            const uint32_t* target_index, size_t n, uint64_t first_id, unsigned gens,
+                            unsigned stable_interval, lifeb200_hit* hits, size_t cap, unsigned long long* n_hits) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (!n_hits) return set_error(LIFEB200_E_ARG, "null n_hits");
+  if (stable_interval == 0) return set_error(LIFEB200_E_ARG, "stable_interval must be >= 1");
+  LIFEB200_CUDA(cudaMemsetAsync(n_hits, 0, sizeof(unsigned long long), ctx->stream));
+  if (n == 0) return LIFEB200_OK;
+  if (!patterns || !targets || (!hits && cap)) return set_error(LIFEB200_E_ARG, "null pointer");
+  if (!aligned16(patterns) || !aligned16(targets)) return set_error(LIFEB200_E_ARG, "pointers must be 16-byte aligned");
+  int lpp = match_lpp(ctx);
+  LIFEB200_DISPATCH_LPP(lpp, (step_match_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
+                                 patterns, targets, target_index, n, first_id, gens, stable_interval, hits, cap, n_hits)));
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+static int fetch_hits(lifeb200_ctx* ctx, lifeb200_hit* d_hits, size_t cap, lifeb200_hit* hits, uint64_t* n_hits) {
+  // counters were copied to the pinned mirror and the stream synchronised by the caller
+  uint64_t found = ctx->h_counters[0];
+  if (n_hits) *n_hits = found;
+  if (found > cap) return set_error(LIFEB200_E_OVERFLOW, "hit buffer too small: %llu hits, capacity %llu",
+                                    (unsigned long long)found, (unsigned long long)cap);
+  if (found) {
+    LIFEB200_CUDA(cudaMemcpyAsync(hits, d_hits, found * sizeof(lifeb200_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::sort(hits, hits + found, [](const lifeb200_hit& a, const lifeb200_hit& b) { return a.id < b.id; });
+  }
+  return LIFEB200_OK;
+}
+
+int lifeb200_enumerate_collisions(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts,
+                                  const uint64_t* projectiles, unsigned n_projectiles, uint64_t id_begin,
+                                  uint64_t id_end, unsigned gens, unsigned stable_interval, lifeb200_hit* hits,
+                                  size_t cap, uint64_t* n_hits, uint64_t* n_skipped) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (!catalysts || !projectiles || n_catalysts == 0 || n_projectiles == 0)
+    return set_error(LIFEB200_E_ARG, "empty catalyst / projectile table");
+  if (stable_interval == 0) return set_error(LIFEB200_E_ARG, "stable_interval must be >= 1");
+  const uint64_t total = (uint64_t)n_catalysts * n_projectiles * 4096ull;
+  if (id_end > total) id_end = total;
+  if (n_hits) *n_hits = 0;
+  if (n_skipped) *n_skipped = 0;
+  if (id_begin >= id_end) return LIFEB200_OK;
+  if (!hits && cap) return set_error(LIFEB200_E_ARG, "null hits with non-zero capacity");
+  const uint64_t n = id_end - id_begin;
+
+  // tables: cat | catZOI | proj | projZOI
+  const size_t words = (size_t)(n_catalysts + n_projectiles) * 2 * 64;
+  std::vector<uint64_t> tab(words);
+  uint64_t* h_cat = tab.data();
+  uint64_t* h_cz = h_cat + (size_t)n_catalysts * 64;
+  uint64_t* h_pr = h_cz + (size_t)n_catalysts * 64;
+  uint64_t* h_pz = h_pr + (size_t)n_projectiles * 64;
+  std::copy(catalysts, catalysts + (size_t)n_catalysts * 64, h_cat);
+  std::copy(projectiles, projectiles + (size_t)n_projectiles * 64, h_pr);
+  for (unsigned c = 0; c < n_catalysts; c++) host_zoi(h_cat + (size_t)c * 64, h_cz + (size_t)c * 64);
+  for (unsigned g = 0; g < n_projectiles; g++) host_zoi(h_pr + (size_t)g * 64, h_pz + (size_t)g * 64);
+
+  uint64_t* d_tab = nullptr;
+  lifeb200_hit* d_hits = nullptr;
+  LIFEB200_CUDA(cudaMalloc(&d_tab, words * 8));
+  cudaError_t e = cap ? cudaMalloc(&d_hits, cap * sizeof(lifeb200_hit)) : cudaSuccess;
+  if (e != cudaSuccess) { cudaFree(d_tab); return cuda_fail(e, "cudaMalloc hits", __FILE__, __LINE__); }
+  int rc = LIFEB200_OK;
+  auto body = [&]() -> int {
+    LIFEB200_CUDA(cudaMemcpyAsync(d_tab, tab.data(), words * 8, cudaMemcpyHostToDevice, ctx->stream));
+    LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
+    const uint64_t* d_cat = d_tab;
+    const uint64_t* d_cz = d_cat + (size_t)n_catalysts * 64;
+    const uint64_t* d_pr = d_cz + (size_t)n_catalysts * 64;
+    const uint64_t* d_pz = d_pr + (size_t)n_projectiles * 64;
+    int lpp = match_lpp(ctx);
+    LIFEB200_DISPATCH_LPP(lpp, (enumerate_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
+                                   d_cat, d_cz, d_pr, d_pz, n_projectiles, id_begin, id_end, gens, stable_interval, d_hits,
+                                   cap, ctx->d_counters + 0, ctx->d_counters + 1)));
+    LIFEB200_LAUNCHED(ctx);
+    LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 4 * sizeof(unsigned long long),
+                                  cudaMemcpyDeviceToHost, ctx->stream));
+    LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (n_skipped) *n_skipped = ctx->h_counters[1];
+    return fetch_hits(ctx, d_hits, cap, hits, n_hits);
+  };
+  rc = body();
+  cudaFree(d_tab);
+  if (d_hits) cudaFree(d_hits);
+  return rc;
+}
+
+int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t seed, int dist, unsigned gens,
+                         lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* pop_sum, uint64_t* hash_xor) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (gens < 2) return set_error(LIFEB200_E_ARG, "survey needs gens >= 2");
+  if (dist != 0 && dist != 1) return set_error(LIFEB200_E_ARG, "dist must be 0 or 1");
+  if (n_hits) *n_hits = 0;
+  if (pop_sum) *pop_sum = 0;
+  if (hash_xor) *hash_xor = 0;
+  if (n == 0) return LIFEB200_OK;
+  if (!hits && cap) return set_error(LIFEB200_E_ARG, "null hits with non-zero capacity");
+  lifeb200_hit* d_hits = nullptr;
+  if (cap) LIFEB200_CUDA(cudaMalloc(&d_hits, cap * sizeof(lifeb200_hit)));
+  auto body = [&]() -> int {
+    LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
+    int lpp = survey_lpp(ctx);
+    LIFEB200_DISPATCH_LPP(lpp, (survey_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
+                                   first_id, n, seed, dist, gens, d_hits, cap, ctx->d_counters + 0, ctx->d_counters + 2,
+                                   ctx->d_counters + 3)));
+    LIFEB200_LAUNCHED(ctx);
+    LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 4 * sizeof(unsigned long long),
+                                  cudaMemcpyDeviceToHost, ctx->stream));
+    LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (pop_sum) *pop_sum = ctx->h_counters[2];
+    if (hash_xor) *hash_xor = ctx->h_counters[3];
+    return fetch_hits(ctx, d_hits, cap, hits, n_hits);
+  };
+  int rc = body();
+  if (d_hits) cudaFree(d_hits);
+  return rc;
+}
+
+int lifeb200_fold_dev(lifeb200_ctx* ctx, const uint64_t* patterns, size_t n, uint64_t first_id, uint64_t* pop_sum,
+                      uint64_t* hash_xor) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (pop_sum) *pop_sum = 0;
+  if (hash_xor) *hash_xor = 0;
+  if (n == 0) return LIFEB200_OK;
+  if (!patterns || !aligned16(patterns)) return set_error(LIFEB200_E_ARG, "bad pattern pointer");
+  LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
+  fold_kernel<8><<<grid_m(n, 8), kBlockM, 0, ctx->stream>>>(patterns, n, first_id, ctx->d_counters + 2,
+                                                              ctx->d_counters + 3);
+  LIFEB200_LAUNCHED(ctx);
+  LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
+                                ctx->stream));
+  LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (pop_sum) *pop_sum = ctx->h_counters[2];
+  if (hash_xor) *hash_xor = ctx->h_counters[3];
+  return LIFEB200_OK;
+}
+
+}  // extern "C"

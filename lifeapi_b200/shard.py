@@ -1,0 +1,68 @@
+"""Batch sharding and the hit-list gather.
+
+Patterns are independent and the 64x64 torus is closed, so the stepping path needs no exchange:
+rank r of R owns the contiguous id range [r*n/R, (r+1)*n/R).  The only collective is one small
+gather per batch: fixed-size counters (all_gather) and the variable-length hit lists (padded
+all_gather), over NCCL on the GPU box and over gloo in the CPU tests.  torch.distributed is
+plumbing here; no tensor maths happens in this file.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .capi import HIT_DTYPE
+
+
+def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:
+    """Contiguous id range of `rank` (same split as the CPU baseline's thread chunks)."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError(f"bad rank/world {rank}/{world}")
+    return n * rank // world, n * (rank + 1) // world
+
+
+def merge_hits(per_rank: list[np.ndarray]) -> np.ndarray:
+    """Concatenate per-rank hit records and sort by id (deterministic order for comparison)."""
+    parts = [np.asarray(h, dtype=HIT_DTYPE) for h in per_rank if len(h)]
+    if not parts:
+        return np.zeros(0, dtype=HIT_DTYPE)
+    allh = np.concatenate(parts)
+    return np.sort(allh, order="id")
+
+
+def gather_hits(hits: np.ndarray, counters: list[int], device=None, group=None):
+    """All ranks call this with their local sorted hits and a list of integer counters.
+
+    Returns (merged_hits, summed_counters, xor_counters) on every rank.  Two collectives:
+    all_gather of [n_hits, counters...] (fixed size), then all_gather of the hit records padded to
+    the largest count (hit lists are KBs..MBs; NVLink bandwidth is irrelevant, latency is one
+    collective per batch).
+    """
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    dev = device if device is not None else torch.device("cpu")
+    hits = np.ascontiguousarray(np.asarray(hits, dtype=HIT_DTYPE))
+    head = torch.tensor([len(hits)] + [int(c) & 0x7FFFFFFFFFFFFFFF for c in counters] +
+                        [int(c) >> 63 for c in counters], dtype=torch.int64, device=dev)
+    heads = [torch.zeros_like(head) for _ in range(world)]
+    dist.all_gather(heads, head, group=group)
+    heads_np = [h.cpu().numpy() for h in heads]
+    k = len(counters)
+    counts = [int(h[0]) for h in heads_np]
+    per_rank_counters = [[int(h[1 + j]) | (int(h[1 + k + j]) << 63) for j in range(k)] for h in heads_np]
+    sums = [sum(c[j] for c in per_rank_counters) & 0xFFFFFFFFFFFFFFFF for j in range(k)]
+    xors = [0] * k
+    for c in per_rank_counters:
+        for j in range(k):
+            xors[j] ^= c[j]
+    maxc = max(counts) if counts else 0
+    if maxc == 0:
+        return np.zeros(0, dtype=HIT_DTYPE), sums, xors
+    pad = np.zeros(maxc, dtype=HIT_DTYPE)
+    pad[: len(hits)] = hits
+    send = torch.from_numpy(pad.view(np.int64).copy()).to(dev)  # 2 x int64 per record
+    recv = [torch.zeros_like(send) for _ in range(world)]
+    dist.all_gather(recv, send, group=group)
+    parts = [r.cpu().numpy().view(HIT_DTYPE)[:c] for r, c in zip(recv, counts)]
+    return merge_hits(parts), sums, xors

@@ -1,0 +1,317 @@
+"""oracle/loader.py -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+ctypes loaders for the two checkers:
+  * Port  : oracle/life_oracle.c + circuits_oracle.c (C restatement; built on demand with gcc)
+  * Ref   : oracle/_ref/libliferef_{v2,v3,v4}.so = the UNMODIFIED reference headers compiled in
+            the build container (prebuilt binary; None if absent).
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+Nothing under lifeapi_b200/ does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PORT_SO = os.path.join(HERE, "_build", "liblifeoracle.so")
+REF_DIR = os.path.join(HERE, "_ref")
+
+_u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+_u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+_u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+
+
+def aligned_copy(a: np.ndarray, align: int = 64) -> np.ndarray:
+    """C-contiguous uint64 copy whose data pointer is `align`-byte aligned (LifeState is alignas(64))."""
+    a = np.asarray(a, dtype=np.uint64)
+    raw = np.empty(a.size * 8 + align, dtype=np.uint8)
+    off = (-raw.ctypes.data) % align
+    out = raw[off:off + a.size * 8].view(np.uint64).reshape(a.shape)
+    out[...] = a
+    return out
+
+
+def build_port(force: bool = False) -> str:
+    srcs = [os.path.join(HERE, "life_oracle.c"), os.path.join(HERE, "circuits_oracle.c")]
+    if force or not os.path.exists(PORT_SO) or any(os.path.getmtime(s) > os.path.getmtime(PORT_SO) for s in srcs):
+        subprocess.run(["make", "-C", HERE, "port"], check=True, stdout=subprocess.DEVNULL)
+    return PORT_SO
+
+
+def build_ref() -> bool:
+    """Compile the reference where it lies (only possible where /root/reference exists)."""
+    if not os.path.isdir("/root/reference"):
+        return False
+    subprocess.run(["make", "-C", HERE, "ref"], check=True, stdout=subprocess.DEVNULL)
+    return True
+
+
+def _cpu_flags() -> set[str]:
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("flags"):
+                return set(line.split(":", 1)[1].split())
+    except OSError:
+        pass
+    return set()
+
+
+def ref_path() -> str | None:
+    flags = _cpu_flags()
+    order = []
+    if {"avx512f", "avx512bw", "avx512vl", "avx512dq", "avx512cd"} <= flags:
+        order.append("v4")
+    if {"avx2", "bmi2", "fma"} <= flags:
+        order.append("v3")
+    order.append("v2")
+    for lvl in order:
+        p = os.path.join(REF_DIR, f"libliferef_{lvl}.so")
+        if os.path.exists(p):
+            return p
+    return None
+
+
+def _sig(lib, name, res, args):
+    fn = getattr(lib, name)
+    fn.restype = res
+    fn.argtypes = args
+    return fn
+
+
+class Port:
+    """The C restatement (kind = "port")."""
+
+    kind = "port"
+
+    def __init__(self):
+        lib = C.CDLL(build_port())
+        self.lib = lib
+        _sig(lib, "lo_step", None, [_u64p])
+        _sig(lib, "lo_step_alt", None, [_u64p])
+        _sig(lib, "lo_step_naive", None, [_u64p])
+        _sig(lib, "lo_step_n", None, [_u64p, C.c_uint])
+        _sig(lib, "lo_step_batch", None, [_u64p, C.c_size_t, C.c_uint, C.c_int])
+        _sig(lib, "lo_max_threads", C.c_int, [])
+        _sig(lib, "lo_neighbour_count", None, [_u64p, _u64p])
+        _sig(lib, "lo_nc_add", None, [_u64p, _u64p, _u64p, _u64p])
+        _sig(lib, "lo_nc_subtract", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "lo_nc_with_exactly", None, [_u64p, C.c_uint, _u64p])
+        _sig(lib, "lo_zoi", None, [_u64p, _u64p])
+        _sig(lib, "lo_target_from_state", None, [_u64p, _u64p])
+        _sig(lib, "lo_contains_target", C.c_int, [_u64p, _u64p])
+        _sig(lib, "lo_moved", None, [_u64p, C.c_int, C.c_int, _u64p])
+        _sig(lib, "lo_pop", C.c_uint, [_u64p])
+        _sig(lib, "lo_soup", None, [_u64p, C.c_uint64, C.c_size_t, C.c_uint64, C.c_int])
+        _sig(lib, "lo_step_match", C.c_int, [_u64p, _u64p, C.c_uint, C.c_uint, C.POINTER(C.c_uint), C.POINTER(C.c_uint)])
+        _sig(lib, "lo_unknown_step", None, [_u64p, _u64p])
+        _sig(lib, "lo_unknown_step_batch", None, [_u64p, _u64p, C.c_size_t, C.c_uint, C.c_int])
+        _sig(lib, "lo_fold_batch", None, [_u64p, C.c_size_t, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)])
+        _sig(lib, "lo_enumerate", C.c_size_t, [_u64p, C.c_uint, _u64p, C.c_uint, C.c_uint64, C.c_uint64, C.c_uint, C.c_uint,
+                                               _u64p, _u32p, _u32p, C.c_size_t, C.POINTER(C.c_uint64)])
+        _sig(lib, "lo_survey", C.c_size_t, [C.c_uint64, C.c_size_t, C.c_uint64, C.c_int, C.c_uint, _u64p, _u32p, C.c_size_t,
+                                            C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)])
+
+    # -- helpers returning fresh arrays ---------------------------------------------------------
+    def threads(self) -> int:
+        return self.lib.lo_max_threads()
+
+    def soup(self, first_id: int, n: int, seed: int, dist: int = 0) -> np.ndarray:
+        out = np.empty((n, 64), dtype=np.uint64)
+        self.lib.lo_soup(out, first_id, n, seed, dist)
+        return out
+
+    def step_batch(self, states: np.ndarray, gens: int, threads: int = 0) -> np.ndarray:
+        out = np.ascontiguousarray(states, dtype=np.uint64).copy()
+        self.lib.lo_step_batch(out.reshape(-1), out.size // 64, gens, threads)
+        return out
+
+    def step(self, s: np.ndarray, kind: str = "step") -> np.ndarray:
+        out = np.ascontiguousarray(s, dtype=np.uint64).copy()
+        getattr(self.lib, {"step": "lo_step", "alt": "lo_step_alt", "naive": "lo_step_naive"}[kind])(out)
+        return out
+
+    def neighbour_count(self, s: np.ndarray) -> np.ndarray:
+        out = np.empty((4, 64), dtype=np.uint64)
+        self.lib.lo_neighbour_count(np.ascontiguousarray(s, dtype=np.uint64), out.reshape(-1))
+        return out
+
+    def zoi(self, s):
+        out = np.empty(64, dtype=np.uint64)
+        self.lib.lo_zoi(np.ascontiguousarray(s, dtype=np.uint64), out)
+        return out
+
+    def moved(self, s, x, y):
+        out = np.empty(64, dtype=np.uint64)
+        self.lib.lo_moved(np.ascontiguousarray(s, dtype=np.uint64), x, y, out)
+        return out
+
+    def target_from_state(self, s):
+        out = np.empty(128, dtype=np.uint64)
+        self.lib.lo_target_from_state(np.ascontiguousarray(s, dtype=np.uint64), out)
+        return out
+
+    def contains_target(self, s, target) -> bool:
+        return bool(self.lib.lo_contains_target(np.ascontiguousarray(s, dtype=np.uint64),
+                                                np.ascontiguousarray(target, dtype=np.uint64).reshape(-1)))
+
+    def pop(self, s) -> int:
+        return self.lib.lo_pop(np.ascontiguousarray(s, dtype=np.uint64))
+
+    def step_match(self, s, target, gens, stable_interval):
+        st = np.ascontiguousarray(s, dtype=np.uint64).copy()
+        a, b = C.c_uint(), C.c_uint()
+        hit = self.lib.lo_step_match(st, np.ascontiguousarray(target, dtype=np.uint64).reshape(-1), gens, stable_interval,
+                                     C.byref(a), C.byref(b))
+        return (a.value, b.value) if hit else None
+
+    def unknown_step_batch(self, state, unknown, gens, threads: int = 0):
+        s = np.ascontiguousarray(state, dtype=np.uint64).copy()
+        u = np.ascontiguousarray(unknown, dtype=np.uint64).copy()
+        self.lib.lo_unknown_step_batch(s.reshape(-1), u.reshape(-1), s.size // 64, gens, threads)
+        return s, u
+
+    def fold_batch(self, states, first_id: int = 0):
+        st = np.ascontiguousarray(states, dtype=np.uint64).reshape(-1)
+        ps, hx = C.c_uint64(), C.c_uint64()
+        self.lib.lo_fold_batch(st, st.size // 64, first_id, C.byref(ps), C.byref(hx))
+        return ps.value, hx.value
+
+    def enumerate(self, catalysts, projectiles, id_begin, id_end, gens, stable_interval, cap, fn="lo_enumerate", lib=None):
+        cat = np.ascontiguousarray(catalysts, dtype=np.uint64).reshape(-1)
+        pro = np.ascontiguousarray(projectiles, dtype=np.uint64).reshape(-1)
+        ids = np.zeros(max(cap, 1), dtype=np.uint64)
+        ff = np.zeros(max(cap, 1), dtype=np.uint32)
+        rec = np.zeros(max(cap, 1), dtype=np.uint32)
+        ns = C.c_uint64()
+        nh = getattr(lib or self.lib, fn)(cat, cat.size // 64, pro, pro.size // 64, id_begin, id_end, gens,
+                                          stable_interval, ids, ff, rec, cap, C.byref(ns))
+        nh = min(nh, cap)
+        return ids[:nh], ff[:nh], rec[:nh], ns.value
+
+    def survey(self, first_id, n, seed, dist, gens, cap):
+        ids = np.zeros(max(cap, 1), dtype=np.uint64)
+        pops = np.zeros(max(cap, 1), dtype=np.uint32)
+        ps, hx = C.c_uint64(), C.c_uint64()
+        nh = self.lib.lo_survey(first_id, n, seed, dist, gens, ids, pops, cap, C.byref(ps), C.byref(hx))
+        nh = min(nh, cap)
+        return ids[:nh], pops[:nh], ps.value, hx.value
+
+
+class Ref:
+    """The unmodified reference compiled here (kind = "reference"); Ref.load() is None if absent."""
+
+    kind = "reference"
+
+    @staticmethod
+    def load() -> "Ref | None":
+        p = ref_path()
+        return Ref(p) if p else None
+
+    def __init__(self, path: str):
+        lib = C.CDLL(path)
+        self.lib = lib
+        self.path = path
+        _sig(lib, "ref_isa", C.c_char_p, [])
+        _sig(lib, "ref_step_batch", None, [_u64p, C.c_size_t, C.c_uint, C.c_int])
+        _sig(lib, "ref_hardware_threads", C.c_int, [])
+        _sig(lib, "ref_step", None, [_u64p])
+        _sig(lib, "ref_step_alt", None, [_u64p])
+        _sig(lib, "ref_step_n", None, [_u64p, C.c_uint])
+        _sig(lib, "ref_hash", C.c_uint64, [_u64p])
+        _sig(lib, "ref_pop", C.c_uint, [_u64p])
+        _sig(lib, "ref_parse", None, [C.c_char_p, _u64p])
+        _sig(lib, "ref_parse_at", None, [C.c_char_p, C.c_int, C.c_int, _u64p])
+        _sig(lib, "ref_moved", None, [_u64p, C.c_int, C.c_int, _u64p])
+        _sig(lib, "ref_zoi", None, [_u64p, _u64p])
+        _sig(lib, "ref_neighbour_count", None, [_u64p, _u64p])
+        _sig(lib, "ref_count_neighbourhood", None, [_u64p, _u64p])
+        _sig(lib, "ref_nc_add", None, [_u64p, _u64p, _u64p, _u64p])
+        _sig(lib, "ref_nc_subtract", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "ref_nc_with_exactly", None, [_u64p, C.c_uint, _u64p])
+        _sig(lib, "ref_target_from_state", None, [_u64p, _u64p])
+        _sig(lib, "ref_contains_target", C.c_int, [_u64p, _u64p])
+        _sig(lib, "ref_step_match", C.c_int, [_u64p, _u64p, C.c_uint, C.c_uint, C.POINTER(C.c_uint), C.POINTER(C.c_uint)])
+        _sig(lib, "ref_unknown_step", None, [_u64p, _u64p])
+        _sig(lib, "ref_unknown_step_batch", None, [_u64p, _u64p, C.c_size_t, C.c_uint, C.c_int])
+        _sig(lib, "ref_enumerate", C.c_size_t, [_u64p, C.c_uint, _u64p, C.c_uint, C.c_uint64, C.c_uint64, C.c_uint, C.c_uint,
+                                                _u64p, _u32p, _u32p, C.c_size_t, C.POINTER(C.c_uint64)])
+        _sig(lib, "ref_survey_states", None, [_u64p, C.c_size_t, C.c_uint, _u8p, _u32p])
+
+    def isa(self) -> str:
+        return self.lib.ref_isa().decode()
+
+    def threads(self) -> int:
+        return self.lib.ref_hardware_threads()
+
+    def parse(self, rle: str, dx: int = 0, dy: int = 0) -> np.ndarray:
+        out = np.empty(64, dtype=np.uint64)
+        self.lib.ref_parse_at(rle.encode(), dx, dy, out)
+        return out
+
+    def step_batch(self, states: np.ndarray, gens: int, threads: int = 0) -> np.ndarray:
+        out = aligned_copy(states)
+        self.lib.ref_step_batch(out.reshape(-1), out.size // 64, gens, threads)
+        return out
+
+    def step(self, s, kind="step"):
+        out = np.ascontiguousarray(s, dtype=np.uint64).copy()
+        getattr(self.lib, {"step": "ref_step", "alt": "ref_step_alt"}[kind])(out)
+        return out
+
+    def hash(self, s) -> int:
+        return self.lib.ref_hash(np.ascontiguousarray(s, dtype=np.uint64))
+
+    def pop(self, s) -> int:
+        return self.lib.ref_pop(np.ascontiguousarray(s, dtype=np.uint64))
+
+    def neighbour_count(self, s, fn="ref_neighbour_count"):
+        out = np.empty((4, 64), dtype=np.uint64)
+        getattr(self.lib, fn)(np.ascontiguousarray(s, dtype=np.uint64), out.reshape(-1))
+        return out
+
+    def zoi(self, s):
+        out = np.empty(64, dtype=np.uint64)
+        self.lib.ref_zoi(np.ascontiguousarray(s, dtype=np.uint64), out)
+        return out
+
+    def moved(self, s, x, y):
+        out = np.empty(64, dtype=np.uint64)
+        self.lib.ref_moved(np.ascontiguousarray(s, dtype=np.uint64), x, y, out)
+        return out
+
+    def target_from_state(self, s):
+        out = np.empty(128, dtype=np.uint64)
+        self.lib.ref_target_from_state(np.ascontiguousarray(s, dtype=np.uint64), out)
+        return out
+
+    def contains_target(self, s, target) -> bool:
+        return bool(self.lib.ref_contains_target(np.ascontiguousarray(s, dtype=np.uint64),
+                                                 np.ascontiguousarray(target, dtype=np.uint64).reshape(-1)))
+
+    def step_match(self, s, target, gens, stable_interval):
+        st = np.ascontiguousarray(s, dtype=np.uint64).copy()
+        a, b = C.c_uint(), C.c_uint()
+        hit = self.lib.ref_step_match(st, np.ascontiguousarray(target, dtype=np.uint64).reshape(-1), gens, stable_interval,
+                                      C.byref(a), C.byref(b))
+        return (a.value, b.value) if hit else None
+
+    def unknown_step_batch(self, state, unknown, gens, threads: int = 0):
+        s = np.ascontiguousarray(state, dtype=np.uint64).copy()
+        u = np.ascontiguousarray(unknown, dtype=np.uint64).copy()
+        self.lib.ref_unknown_step_batch(s.reshape(-1), u.reshape(-1), s.size // 64, gens, threads)
+        return s, u
+
+    def enumerate(self, catalysts, projectiles, id_begin, id_end, gens, stable_interval, cap):
+        return Port.enumerate(self, catalysts, projectiles, id_begin, id_end, gens, stable_interval, cap,
+                              fn="ref_enumerate", lib=self.lib)
+
+    def survey_states(self, states, gens):
+        st = np.ascontiguousarray(states, dtype=np.uint64).copy()
+        n = st.size // 64
+        act = np.zeros(n, dtype=np.uint8)
+        pop = np.zeros(n, dtype=np.uint32)
+        self.lib.ref_survey_states(st.reshape(-1), n, gens, act, pop)
+        return st, act, pop

@@ -1,0 +1,114 @@
+"""GPU parity tests of the fused step + LifeTarget match, collision enumeration and soup survey."""
+import numpy as np
+import pytest
+
+from conftest import SEED, golden
+
+pytestmark = pytest.mark.gpu
+
+
+def test_step_match_vs_oracle(engine, port):
+    c = golden("collisions.npz")
+    cats, targets, gl = c["catalysts"], c["targets"], c["gliders"]
+    rng = np.random.default_rng(3)
+    n = 1500
+    pats = np.empty((n, 64), dtype=np.uint64)
+    tidx = rng.integers(0, len(cats), size=n).astype(np.uint32)
+    for p in range(n):
+        dx, dy = rng.integers(14, 44, size=2)
+        pats[p] = cats[tidx[p]] | port.moved(gl[rng.integers(0, 32)], int(dx) - 8, int(dy) - 8)
+    for lpp in (4, 8, 32):
+        engine.set_lanes_per_pattern(lpp)
+        try:
+            hits = engine.step_match(pats, targets, tidx, gens=160, stable_interval=6, first_id=1000)
+        finally:
+            engine.set_lanes_per_pattern(0)
+        want = []
+        for p in range(n):
+            r = port.step_match(pats[p], targets[tidx[p]], 160, 6)
+            if r:
+                want.append((1000 + p, r[0], r[1]))
+        assert len(want) > 20
+        assert [(int(h["id"]), int(h["g_first_false"]), int(h["g_recovered"])) for h in hits] == want, lpp
+
+
+def test_step_match_single_target_and_overflow(engine, port):
+    from lifeapi_b200 import E_ARG, E_OVERFLOW, LifeB200Error
+    c = golden("collisions.npz")
+    cat, tgt, gl = c["catalysts"][0], c["targets"][0], c["gliders"]
+    pats = np.stack([cat | port.moved(gl[k % 32], 10 + k % 17, 12 + k % 13) for k in range(400)])
+    hits = engine.step_match(pats, tgt[None], None, 128, 4)
+    want = [k for k in range(400) if port.step_match(pats[k], tgt, 128, 4)]
+    assert list(hits["id"]) == want and len(want) >= 2
+    with pytest.raises(LifeB200Error) as ei:
+        engine.step_match(pats, tgt[None], None, 128, 4, cap=1)
+    assert ei.value.code == E_OVERFLOW
+    with pytest.raises(LifeB200Error) as ei:
+        engine.step_match(pats, tgt[None], None, 128, 0)
+    assert ei.value.code == E_ARG
+    assert len(engine.step_match(pats[:0], tgt[None], None, 10, 2)) == 0
+
+
+def test_enumeration_vs_reference_golden(engine):
+    """The golden list was produced by reference calls only (ZOI, Moved, |, Step, Contains)."""
+    from lifeapi_b200 import E_OVERFLOW, LifeB200Error
+    c = golden("collisions.npz")
+    n_cat = int(c["enum_n_cat"])
+    total = n_cat * 32 * 4096
+    hits, skipped = engine.enumerate_collisions(c["catalysts"][:n_cat], c["gliders"], 0, total, int(c["enum_gens"]),
+                                                int(c["enum_interval"]), cap=1 << 16)
+    assert skipped == int(c["enum_skipped"])
+    assert (hits["id"] == c["enum_ids"]).all()
+    assert (hits["g_first_false"] == c["enum_first_false"]).all()
+    assert (hits["g_recovered"] == c["enum_recovered"]).all()
+    # shards of the id space concatenate to the same list (multi-GPU partitioning)
+    from lifeapi_b200 import merge_hits, shard_range
+    parts, sk = [], 0
+    for r in range(3):
+        lo, hi = shard_range(total, r, 3)
+        h, s = engine.enumerate_collisions(c["catalysts"][:n_cat], c["gliders"], lo, hi, int(c["enum_gens"]),
+                                           int(c["enum_interval"]), cap=1 << 16)
+        parts.append(h)
+        sk += s
+    assert sk == skipped and (merge_hits(parts) == hits).all()
+    with pytest.raises(LifeB200Error) as ei:
+        engine.enumerate_collisions(c["catalysts"][:n_cat], c["gliders"], 0, total, int(c["enum_gens"]),
+                                    int(c["enum_interval"]), cap=10)
+    assert ei.value.code == E_OVERFLOW
+
+
+def test_enumeration_vs_oracle_other_catalysts(engine, port):
+    c = golden("collisions.npz")
+    cats = c["catalysts"]
+    lo, hi = 4 * 32 * 4096 + 7, 4 * 32 * 4096 + 3 * 4096 + 11  # beehive, ragged range over 3+ glider variants
+    for lpp in (4, 16):
+        engine.set_lanes_per_pattern(lpp)
+        try:
+            hits, skipped = engine.enumerate_collisions(cats, c["gliders"], lo, hi, 100, 5, cap=1 << 14)
+        finally:
+            engine.set_lanes_per_pattern(0)
+        ids, ff, rec, sk = port.enumerate(cats, c["gliders"], lo, hi, 100, 5, 1 << 14)
+        assert skipped == sk
+        assert (hits["id"] == ids).all() and (hits["g_first_false"] == ff).all() and (hits["g_recovered"] == rec).all()
+
+
+def test_soup_survey_vs_oracle(engine, port):
+    for (first, n, dist, gens, lpp) in [(0, 333, 0, 300, 8), (1 << 33, 1000, 1, 130, 2), (17, 64, 0, 2, 32), (5, 257, 0, 64, 16)]:
+        engine.set_lanes_per_pattern(lpp)
+        try:
+            hits, ps, hx = engine.soup_survey(first, n, SEED, dist, gens, cap=n)
+        finally:
+            engine.set_lanes_per_pattern(0)
+        ids, pops, ps_o, hx_o = port.survey(first, n, SEED, dist, gens, n)
+        assert (hits["id"] == ids).all() and (hits["g_first_false"] == pops).all()
+        assert (ps, hx) == (ps_o, hx_o)
+
+
+def test_fold_matches_oracle(engine, port):
+    soups = port.soup(50, 999, SEED)
+    d = engine.malloc(soups.nbytes)
+    try:
+        engine.h2d(d, soups)
+        assert engine.fold_dev(d, 999, 50) == port.fold_batch(soups, 50)
+    finally:
+        engine.free(d)

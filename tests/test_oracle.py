@@ -1,0 +1,174 @@
+"""CPU tests: pin the oracle (C restatement) against the reference's known answers, the golden
+vectors produced by the unmodified reference, and -- when oracle/_ref is present -- the reference
+itself, differentially (the pattern of tests/StepAltTest.cpp:5-13: seeded random states, bit-exact ==)."""
+import numpy as np
+import pytest
+
+from conftest import SEED, golden
+
+# SURVEY.md 8(c) / BASELINE.md 5: reference Step() on LifeState::Parse("b2o$2o$bo!")
+KNOWN = {1: (6, 0x0549DE903160DDAF), 2: (7, 0x5ACAA23574BB6D97), 10: (11, 0x4D9E729E7A379063),
+         100: (121, 0x03517B63993A38C3), 256: (76, 0x50ABDA84234A962D), 500: (247, 0x6559805396198161),
+         1000: (113, 0xDC35D1573487DC91), 1024: (113, 0xDC35D1573487DC91)}
+
+
+def test_golden_matches_survey_known_answers():
+    g = golden("rpentomino.npz")
+    gens = list(g["gens"])
+    for gen, (pop, h) in KNOWN.items():
+        i = gens.index(gen)
+        assert int(g["pops"][i]) == pop
+        assert int(g["xxh3"][i]) == h
+    s = golden("soups.npz")
+    assert int(s["mt1_pop0"]) == 2014 and int(s["mt1_pop"]) == 340
+    assert int(s["mt1_xxh3"]) == 0x77B09695A0065A59
+    assert int(s["mt42_xor_xxh3"]) == 0xA0384537038C7533
+
+
+def test_port_rpentomino_every_generation(port):
+    g = golden("rpentomino.npz")
+    want = {int(k): g["states"][i] for i, k in enumerate(g["gens"])}
+    cur = want[0].copy()
+    assert port.pop(cur) == 5
+    for gen in range(1, 1025):
+        nxt = port.step(cur)
+        assert (nxt == port.step(cur, "alt")).all()
+        if gen <= 64 or gen % 97 == 0:
+            assert (nxt == port.step(cur, "naive")).all()
+        cur = nxt
+        if gen in want:
+            assert (cur == want[gen]).all(), f"gen {gen}"
+            assert port.pop(cur) == int(g["pops"][list(g["gens"]).index(gen)])
+
+
+def test_port_soups_golden(port):
+    s = golden("soups.npz")
+    assert (port.soup(0, 16, int(s["seed"]), 0) == s["soups0"]).all()
+    assert (port.soup(0, 16, int(s["seed"]), 1) == s["soups1"]).all()
+    # reference-shaped distribution: bits 63,62 clear, bit 61 set (LifeAPI.hpp:21-22)
+    assert (s["soups1"] >> np.uint64(62) == 0).all() and ((s["soups1"] >> np.uint64(61)) & np.uint64(1) == 1).all()
+    for i, k in enumerate(s["gens"]):
+        assert (port.step_batch(s["soups0"], int(k)) == s["stepped0"][i]).all()
+        assert (port.step_batch(s["soups1"], int(k), threads=1) == s["stepped1"][i]).all()
+    assert (port.step_batch(s["mt1"][None], 1024)[0] == s["mt1_final"]).all()
+    assert (port.step_batch(s["mt42_first8"], 1024) == s["mt42_first8_final"]).all()
+
+
+def test_port_planes_golden(port):
+    p = golden("planes.npz")
+    for i in range(8):
+        assert (port.neighbour_count(p["soups"][i]) == p["ncount"][i]).all()
+    for i in range(len(p["zoi_in"])):
+        assert (port.zoi(p["zoi_in"][i]) == p["zoi"][i]).all()
+    for (x, y), want in zip(p["moves"], p["moved"]):
+        assert (port.moved(p["soups"][0], int(x), int(y)) == want).all()
+
+
+def test_port_neighbour_count_is_the_3x3_sum(port):
+    s = port.soup(7, 1, SEED)[0]
+    planes = port.neighbour_count(s)  # bit3, bit2, bit1, bit0
+    bits = ((s[:, None] >> np.arange(64, dtype=np.uint64)[None, :]) & np.uint64(1)).astype(np.int64)  # [x, y]
+    total = sum(np.roll(np.roll(bits, dx, 0), dy, 1) for dx in (-1, 0, 1) for dy in (-1, 0, 1))
+    got = sum(((planes[3 - k][:, None] >> np.arange(64, dtype=np.uint64)[None, :]) & np.uint64(1)).astype(np.int64) << k
+              for k in range(4))
+    assert (got == total).all()
+
+
+def test_port_collisions_golden(port):
+    c = golden("collisions.npz")
+    for cat, tgt in zip(c["catalysts"], c["targets"]):
+        assert (port.target_from_state(cat) == tgt).all()
+        assert port.contains_target(cat, tgt)
+    n_cat = int(c["enum_n_cat"])
+    # a slice of the id space (the whole space is checked on the GPU): first catalyst, 3 glider variants
+    lo, hi = 0, 3 * 4096
+    ids, ff, rec, skipped = port.enumerate(c["catalysts"][:n_cat], c["gliders"], lo, hi, int(c["enum_gens"]),
+                                           int(c["enum_interval"]), 1 << 16)
+    sel = (c["enum_ids"] >= lo) & (c["enum_ids"] < hi)
+    assert (ids == c["enum_ids"][sel]).all()
+    assert (ff == c["enum_first_false"][sel]).all() and (rec == c["enum_recovered"][sel]).all()
+
+
+def test_port_unknown_step_golden(port):
+    u = golden("unknown_step.npz")
+    assert not (u["state"] & u["unknown"]).any()
+    for i, k in enumerate(u["gens"]):
+        s, k_ = port.unknown_step_batch(u["state"], u["unknown"], int(k))
+        assert (s == u["next_state"][i]).all(), f"state after {k} gens"
+        assert (k_ == u["next_unknown"][i]).all(), f"unknown after {k} gens"
+        assert not (s & k_).any()
+
+
+def test_port_unknown_step_reduces_to_life_without_unknowns(port):
+    s = port.soup(3, 4, SEED)
+    z = np.zeros_like(s)
+    a, b = port.unknown_step_batch(s, z, 5)
+    assert (a == port.step_batch(s, 5)).all() and not b.any()
+
+
+# ---- differential against the compiled reference (this container only) -------------------------
+
+def test_port_vs_reference_step_random(port, ref):
+    """tests/StepAltTest.cpp shape: many random states, Step == StepAlt == port, bit-exact."""
+    n = 2000
+    soups = np.concatenate([port.soup(10_000, n // 2, SEED, 0), port.soup(20_000, n // 2, SEED, 1)])
+    for g in (1, 2, 7):
+        assert (port.step_batch(soups, g) == ref.step_batch(soups, g)).all()
+    for s in soups[:200]:
+        r = ref.step(s)
+        assert (r == ref.step(s, "alt")).all() and (r == port.step(s)).all() and (r == port.step(s, "alt")).all()
+
+
+def test_port_vs_reference_planes_and_targets(port, ref):
+    soups = port.soup(500, 64, SEED, 0)
+    sparse = soups & port.soup(600, 64, SEED, 0) & port.soup(700, 64, SEED, 0)
+    for s in list(soups[:32]) + list(sparse[:32]):
+        assert (port.neighbour_count(s) == ref.neighbour_count(s)).all()
+        assert (port.zoi(s) == ref.zoi(s)).all()
+        t = ref.target_from_state(s)
+        assert (port.target_from_state(s) == t).all()
+        for other in (s, ref.step(s), soups[0]):
+            assert port.contains_target(other, t) == ref.contains_target(other, t)
+        assert port.pop(s) == ref.pop(s)
+    for x, y in [(0, 0), (5, -7), (-64, 64), (100, 3), (-1, -1)]:
+        assert (port.moved(soups[1], x, y) == ref.moved(soups[1], x, y)).all()
+
+
+def test_port_vs_reference_step_match_and_enumerate(port, ref):
+    c = golden("collisions.npz")
+    cats, gl = c["catalysts"], c["gliders"]
+    lo, hi = 5 * 4096 + 100, 5 * 4096 + 1500
+    a = port.enumerate(cats[:3], gl, lo, hi, 96, 4, 4096)
+    b = ref.enumerate(cats[:3], gl, lo, hi, 96, 4, 4096)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    t = ref.target_from_state(cats[0])
+    for gi in range(0, 32, 5):
+        for dx, dy in [(20, 20), (24, 22), (22, 25), (30, 18)]:
+            s = cats[0] | ref.moved(gl[gi], dx, dy)
+            assert port.step_match(s, t, 200, 6) == ref.step_match(s, t, 200, 6)
+
+
+def test_port_vs_reference_unknown_step(port, ref):
+    rng = np.random.default_rng(7)
+    n = 64
+    state = port.soup(4000, n, SEED, 0) & port.soup(5000, n, SEED, 0)
+    unk = rng.integers(0, 1 << 63, size=(n, 64), dtype=np.uint64) & rng.integers(0, 1 << 63, size=(n, 64), dtype=np.uint64) \
+        & rng.integers(0, 1 << 63, size=(n, 64), dtype=np.uint64)
+    unk[: n // 2] &= np.array([ref.zoi(s) for s in state[: n // 2]])
+    state &= ~unk
+    for g in (1, 3):
+        ps, pu = port.unknown_step_batch(state, unk, g)
+        rs, ru = ref.unknown_step_batch(state, unk, g)
+        assert (ps == rs).all() and (pu == ru).all()
+
+
+def test_port_survey_matches_reference_predicates(port, ref):
+    n, gens = 48, 300
+    ids, pops, ps, hx = port.survey(123, n, SEED, 0, gens, n)
+    soups = port.soup(123, n, SEED, 0)
+    final, act, pop = ref.survey_states(soups, gens)
+    assert (np.nonzero(act)[0] + 123 == ids).all()
+    assert (pop[act.astype(bool)] == pops).all()
+    assert int(pop.sum()) == ps
+    assert port.fold_batch(final, 123) == (ps, hx)
