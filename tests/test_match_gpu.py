@@ -7,41 +7,56 @@ from conftest import SEED, golden
 pytestmark = pytest.mark.gpu
 
 
+def placements(port, c, ids):
+    """pattern = catalyst | projectile.Moved(dx, dy) for enumeration ids (include/lifeapi_b200.h)."""
+    cats, gl = c["catalysts"], c["gliders"]
+    pats = np.empty((len(ids), 64), dtype=np.uint64)
+    tidx = np.empty(len(ids), dtype=np.uint32)
+    for k, i in enumerate(ids):
+        i = int(i)
+        dy, dx, cg = i & 63, (i >> 6) & 63, i >> 12
+        tidx[k] = cg // 32
+        pats[k] = cats[cg // 32] | port.moved(gl[cg % 32], dx, dy)
+    return pats, tidx
+
+
 def test_step_match_vs_oracle(engine, port):
     c = golden("collisions.npz")
-    cats, targets, gl = c["catalysts"], c["targets"], c["gliders"]
+    targets = c["targets"]
     rng = np.random.default_rng(3)
-    n = 1500
-    pats = np.empty((n, 64), dtype=np.uint64)
-    tidx = rng.integers(0, len(cats), size=n).astype(np.uint32)
-    for p in range(n):
-        dx, dy = rng.integers(14, 44, size=2)
-        pats[p] = cats[tidx[p]] | port.moved(gl[rng.integers(0, 32)], int(dx) - 8, int(dy) - 8)
-    for lpp in (4, 8, 32):
+    # 300 placements the reference found to be hits + 1200 random ones (mostly misses / overlaps)
+    ids = np.concatenate([rng.choice(c["enum_ids"], 300, replace=False),
+                          rng.integers(0, 8 * 32 * 4096, size=1200).astype(np.uint64)])
+    rng.shuffle(ids)
+    pats, tidx = placements(port, c, ids)
+    n = len(ids)
+    for lpp, gens, interval in ((4, 128, 8), (8, 160, 6), (32, 90, 3)):
         engine.set_lanes_per_pattern(lpp)
         try:
-            hits = engine.step_match(pats, targets, tidx, gens=160, stable_interval=6, first_id=1000)
+            hits = engine.step_match(pats, targets, tidx, gens=gens, stable_interval=interval, first_id=1000)
         finally:
             engine.set_lanes_per_pattern(0)
         want = []
         for p in range(n):
-            r = port.step_match(pats[p], targets[tidx[p]], 160, 6)
+            r = port.step_match(pats[p], targets[tidx[p]], gens, interval)
             if r:
                 want.append((1000 + p, r[0], r[1]))
-        assert len(want) > 20
+        assert len(want) > 100
         assert [(int(h["id"]), int(h["g_first_false"]), int(h["g_recovered"])) for h in hits] == want, lpp
 
 
 def test_step_match_single_target_and_overflow(engine, port):
     from lifeapi_b200 import E_ARG, E_OVERFLOW, LifeB200Error
     c = golden("collisions.npz")
-    cat, tgt, gl = c["catalysts"][0], c["targets"][0], c["gliders"]
-    pats = np.stack([cat | port.moved(gl[k % 32], 10 + k % 17, 12 + k % 13) for k in range(400)])
-    hits = engine.step_match(pats, tgt[None], None, 128, 4)
-    want = [k for k in range(400) if port.step_match(pats[k], tgt, 128, 4)]
-    assert list(hits["id"]) == want and len(want) >= 2
+    tgt = c["targets"][0]
+    first = c["enum_ids"][c["enum_ids"] < 32 * 4096]  # catalyst 0 only
+    ids = np.concatenate([first[:40], np.arange(5000, 5360, dtype=np.uint64)])
+    pats, _ = placements(port, c, ids)
+    hits = engine.step_match(pats, tgt[None], None, 128, 8)
+    want = [k for k in range(len(ids)) if port.step_match(pats[k], tgt, 128, 8)]
+    assert list(hits["id"]) == want and len(want) >= 40
     with pytest.raises(LifeB200Error) as ei:
-        engine.step_match(pats, tgt[None], None, 128, 4, cap=1)
+        engine.step_match(pats, tgt[None], None, 128, 8, cap=1)
     assert ei.value.code == E_OVERFLOW
     with pytest.raises(LifeB200Error) as ei:
         engine.step_match(pats, tgt[None], None, 128, 0)
