@@ -1,0 +1,288 @@
+// LifeAPI_b200.hpp -- drop-in host header for the STEPPING PATH of scorbiclife/LifeAPI, backed by
+// the B200 CUDA library (include/lifeapi_b200.h).  Same type names, member signatures and memory
+// layout as the reference for everything on the path:
+//
+//   LifeState   { uint64_t state[64]; }  alignas(64)          LifeAPI.hpp:39-40
+//       Step(), Step(unsigned), Stepped(), Stepped(unsigned), StepAlt()   :866-886
+//       Contains(const LifeTarget&)                                      LifeTarget.hpp:44-51
+//       HalfAdd / FullAdd (sum, carry by reference first)                 :822-833,850-864
+//   LifeTarget  { wanted, unwanted }                                     LifeTarget.hpp:5-18
+//   NeighbourCount { bit3, bit2, bit1, bit0 }                            NeighbourCount.hpp:7-102
+//   LifeHistory { state, history, marked, original }                     LifeHistory.hpp:8-12
+//
+// Every stepping member is a batch of ONE through the same sm_100a kernels the batched API uses;
+// there is NO CPU implementation of Step in this header and no fallback: if the library cannot
+// create a context (no B200) the process aborts with the library's error message, which is the
+// reference's error model (it has no recoverable errors).
+//
+// Throughput comes from the batched API (LifeBatch below / the C ABI), not from single calls.
+// Plane algebra (operator&,|,^,~, ==, IsEmpty, GetPop, Moved, ZOI, NeighbourCount::Add ...) is
+// host-side value arithmetic exactly as in the reference; it is not part of the accelerated path.
+#pragma once
+
+#include <bit>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "lifeapi_b200.h"
+
+constexpr int N = 64;  // LifeAPI.hpp:12
+
+namespace lifeb200 {
+
+[[noreturn]] inline void Die(const char* what) {
+  std::fprintf(stderr, "LifeAPI_b200: %s: %s\n", what, lifeb200_last_error());
+  std::abort();
+}
+inline void Check(int rc, const char* what) {
+  if (rc != LIFEB200_OK) Die(what);
+}
+
+// Process-wide default context on device $LIFEB200_DEVICE (default 0), created on first use.
+inline lifeb200_ctx* DefaultContext() {
+  static lifeb200_ctx* ctx = [] {
+    const char* e = std::getenv("LIFEB200_DEVICE");
+    lifeb200_ctx* c = nullptr;
+    Check(lifeb200_create(e ? std::atoi(e) : 0, &c), "lifeb200_create");
+    return c;
+  }();
+  return ctx;
+}
+
+}  // namespace lifeb200
+
+struct LifeTarget;
+
+struct alignas(64) LifeState {
+  uint64_t state[N];
+
+  constexpr LifeState() : state{0} {}
+
+  uint64_t& operator[](unsigned i) { return state[i]; }
+  uint64_t operator[](unsigned i) const { return state[i]; }
+
+  // ---- cell access (LifeAPI.hpp:131-146): word = column x, bit = row y ----------------------
+  void Set(unsigned x, unsigned y) { state[x & 63] |= 1ULL << (y & 63); }
+  void Erase(unsigned x, unsigned y) { state[x & 63] &= ~(1ULL << (y & 63)); }
+  bool Get(unsigned x, unsigned y) const { return (state[x & 63] >> (y & 63)) & 1ULL; }
+
+  // ---- plane algebra (LifeAPI.hpp:213-298) --------------------------------------------------
+  bool operator==(const LifeState& o) const { return std::memcmp(state, o.state, sizeof state) == 0; }
+  bool operator!=(const LifeState& o) const { return !(*this == o); }
+  LifeState operator~() const { LifeState r; for (int i = 0; i < N; i++) r.state[i] = ~state[i]; return r; }
+  LifeState operator&(const LifeState& o) const { LifeState r; for (int i = 0; i < N; i++) r.state[i] = state[i] & o.state[i]; return r; }
+  LifeState operator|(const LifeState& o) const { LifeState r; for (int i = 0; i < N; i++) r.state[i] = state[i] | o.state[i]; return r; }
+  LifeState operator^(const LifeState& o) const { LifeState r; for (int i = 0; i < N; i++) r.state[i] = state[i] ^ o.state[i]; return r; }
+  LifeState& operator&=(const LifeState& o) { for (int i = 0; i < N; i++) state[i] &= o.state[i]; return *this; }
+  LifeState& operator|=(const LifeState& o) { for (int i = 0; i < N; i++) state[i] |= o.state[i]; return *this; }
+  LifeState& operator^=(const LifeState& o) { for (int i = 0; i < N; i++) state[i] ^= o.state[i]; return *this; }
+  bool IsEmpty() const { uint64_t a = 0; for (int i = 0; i < N; i++) a |= state[i]; return a == 0; }
+  unsigned GetPop() const { unsigned p = 0; for (int i = 0; i < N; i++) p += (unsigned)std::popcount(state[i]); return p; }
+
+  // ---- geometry used to build placements and targets (LifeAPI.hpp:521-538,699-717) -----------
+  LifeState Moved(int x, int y) const {
+    LifeState r;
+    const unsigned sx = (unsigned)x & 63u;
+    for (unsigned i = 0; i < (unsigned)N; i++) r.state[(i + sx) & 63u] = std::rotl(state[i], y);
+    return r;
+  }
+  void Move(int x, int y) { *this = Moved(x, y); }
+  LifeState ZOI() const {
+    uint64_t col[N];
+    for (int i = 0; i < N; i++) col[i] = state[i] | std::rotl(state[i], 1) | std::rotr(state[i], 1);
+    LifeState r;
+    for (int i = 0; i < N; i++) r.state[i] = col[(i + N - 1) & 63] | col[i] | col[(i + 1) & 63];
+    return r;
+  }
+  LifeState GetBoundary() const { return ZOI() & ~*this; }
+
+  // ---- RLE input (Parsing.hpp:143-198 semantics: a bare '$' counts as one row) ---------------
+  static LifeState Parse(const std::string& rle, int dx = 0, int dy = 0) {
+    LifeState r;
+    int x = 0, y = 0, cnt = 0;
+    for (char ch : rle) {
+      if (ch >= '0' && ch <= '9') { cnt = cnt * 10 + (ch - '0'); continue; }
+      const int k = cnt ? cnt : 1;
+      cnt = 0;
+      if (ch == 'o' || ch == 'A') { for (int j = 0; j < k; j++) r.Set((unsigned)(x + j + dx), (unsigned)(y + dy)); x += k; }
+      else if (ch == 'b' || ch == '.') x += k;
+      else if (ch == '$') { y += k; x = 0; }
+      else if (ch == '!') break;
+    }
+    return r;
+  }
+
+  // ---- adder conventions (LifeAPI.hpp:822-833,850-864): (sum, carry) first, by reference ------
+  static inline void HalfAdd(uint64_t& out0, uint64_t& out1, uint64_t a, uint64_t b) { out0 = a ^ b; out1 = a & b; }
+  static inline void FullAdd(uint64_t& out0, uint64_t& out1, uint64_t a, uint64_t b, uint64_t c) {
+    const uint64_t t = a ^ b;
+    out0 = t ^ c;
+    out1 = (a & b) | (t & c);
+  }
+  static inline void HalfAdd(LifeState& out0, LifeState& out1, const LifeState& a, const LifeState& b) {
+    for (int i = 0; i < N; i++) HalfAdd(out0.state[i], out1.state[i], a.state[i], b.state[i]);
+  }
+  static inline void FullAdd(LifeState& out0, LifeState& out1, const LifeState& a, const LifeState& b, const LifeState& c) {
+    for (int i = 0; i < N; i++) FullAdd(out0.state[i], out1.state[i], a.state[i], b.state[i], c.state[i]);
+  }
+
+  // ---- THE PATH: stepping on the B200 (LifeAPI.hpp:866-886,1196-1254) ------------------------
+  void Step() { Step(1u); }
+  void Step(unsigned numIters) {
+    lifeb200::Check(lifeb200_step_batch_host(lifeb200::DefaultContext(), state, state, 1, numIters), "LifeState::Step");
+  }
+  void StepAlt() { Step(1u); }  // same function, second formulation in the reference (:1218-1254)
+  [[nodiscard]] LifeState Stepped() const { LifeState r = *this; r.Step(); return r; }
+  [[nodiscard]] LifeState Stepped(unsigned numIters) const { LifeState r = *this; r.Step(numIters); return r; }
+
+  // CountNeighbourhood (LifeAPI.hpp:909-952): 3x3 sum including the centre, four planes.
+  void CountNeighbourhood(LifeState& bit3, LifeState& bit2, LifeState& bit1, LifeState& bit0) const {
+    alignas(64) uint64_t planes[4 * N];
+    lifeb200::Check(lifeb200_neighbour_count_host(lifeb200::DefaultContext(), state, planes, 1), "CountNeighbourhood");
+    std::memcpy(bit3.state, planes, 512); std::memcpy(bit2.state, planes + N, 512);
+    std::memcpy(bit1.state, planes + 2 * N, 512); std::memcpy(bit0.state, planes + 3 * N, 512);
+  }
+
+  bool Contains(const LifeTarget& target) const;  // LifeTarget.hpp:44-51 (defined below)
+  bool Contains(const LifeState& pat) const { return (*this & pat) == pat; }                 // :388-397
+  bool AreDisjoint(const LifeState& pat) const { return (*this & pat).IsEmpty(); }          // :377-386
+};
+static_assert(sizeof(LifeState) == 512 && alignof(LifeState) == 64, "LifeState layout (LifeAPI.hpp:39-40)");
+
+struct LifeTarget {
+  LifeState wanted;
+  LifeState unwanted;
+  LifeTarget() = default;
+  explicit LifeTarget(const LifeState& s) : wanted{s}, unwanted{s.GetBoundary()} {}
+  LifeTarget(const LifeState& w, const LifeState& u) : wanted{w}, unwanted{u} {}
+  [[nodiscard]] LifeTarget Moved(std::pair<int, int> v) const { return LifeTarget(wanted.Moved(v.first, v.second), unwanted.Moved(v.first, v.second)); }
+};
+static_assert(sizeof(LifeTarget) == 1024, "LifeTarget layout (LifeTarget.hpp:5-7)");
+
+inline bool LifeState::Contains(const LifeTarget& t) const {
+  uint64_t d = 0;
+  for (int i = 0; i < N; i++) d |= (state[i] ^ t.wanted.state[i]) & (t.wanted.state[i] | t.unwanted.state[i]);
+  return d == 0;
+}
+
+// NeighbourCount.hpp:7-102 -- construction runs on the GPU; Add/Subtract/WithExactly are the
+// reference's ripple plane algebra.
+struct NeighbourCount {
+  LifeState bit3, bit2, bit1, bit0;
+  NeighbourCount() = default;
+  explicit NeighbourCount(const LifeState& s) { s.CountNeighbourhood(bit3, bit2, bit1, bit0); }
+  NeighbourCount Add(const NeighbourCount& o, const LifeState& incarry) const {
+    NeighbourCount r;
+    LifeState carry = incarry;
+    LifeState::FullAdd(r.bit0, carry, bit0, o.bit0, carry);
+    LifeState::FullAdd(r.bit1, carry, bit1, o.bit1, carry);
+    LifeState::FullAdd(r.bit2, carry, bit2, o.bit2, carry);
+    LifeState::FullAdd(r.bit3, carry, bit3, o.bit3, carry);
+    return r;
+  }
+  NeighbourCount operator~() const { NeighbourCount r; r.bit3 = ~bit3; r.bit2 = ~bit2; r.bit1 = ~bit1; r.bit0 = ~bit0; return r; }
+  NeighbourCount operator+(const NeighbourCount& o) const { return Add(o, LifeState()); }
+  NeighbourCount Subtract(const NeighbourCount& o) const { return Add(~o, ~LifeState()); }
+  NeighbourCount operator-(const NeighbourCount& o) const { return Subtract(o); }
+  LifeState WithExactly(unsigned n) const {
+    LifeState r = ~LifeState();
+    r &= (n & 1) ? bit0 : ~bit0;
+    r &= (n & 2) ? bit1 : ~bit1;
+    r &= (n & 4) ? bit2 : ~bit2;
+    r &= (n & 8) ? bit3 : ~bit3;
+    return r;
+  }
+};
+static_assert(sizeof(NeighbourCount) == 2048, "NeighbourCount layout (NeighbourCount.hpp:7-11)");
+
+// LifeHistory.hpp:8-12: passive 4-plane container (no Step in the reference).
+struct LifeHistory {
+  LifeState state, history, marked, original;
+  // build-defined accumulate step: state.Step(n) then history |= state
+  void StepAccumulate(unsigned n = 1) { for (unsigned i = 0; i < n; i++) { state.Step(); history |= state; } }
+};
+
+// ---------------------------------------------------------------------------------------------
+// Batched API: a std::vector<LifeState> is already the flat AoS batch.
+// ---------------------------------------------------------------------------------------------
+struct LifeHit {
+  uint64_t id;
+  uint32_t g_first_false, g_recovered;
+};
+static_assert(sizeof(LifeHit) == sizeof(lifeb200_hit), "hit record layout");
+
+class LifeBatch {
+ public:
+  explicit LifeBatch(lifeb200_ctx* ctx = nullptr) : ctx_(ctx ? ctx : lifeb200::DefaultContext()) {}
+  ~LifeBatch() { if (d_) lifeb200_free(ctx_, d_); }
+  LifeBatch(const LifeBatch&) = delete;
+  LifeBatch& operator=(const LifeBatch&) = delete;
+
+  // batch[i].Step(gens) for every i (LifeAPI.hpp:877-881), host in / host out, pipelined copies
+  static void Step(std::vector<LifeState>& batch, unsigned gens, lifeb200_ctx* ctx = nullptr) {
+    if (batch.empty()) return;
+    lifeb200::Check(lifeb200_step_batch_host(ctx ? ctx : lifeb200::DefaultContext(), batch[0].state, batch[0].state,
+                                             batch.size(), gens), "LifeBatch::Step");
+  }
+
+  // resident batch: upload once, step many times, download when needed
+  void Upload(const std::vector<LifeState>& batch) {
+    Reserve(batch.size());
+    n_ = batch.size();
+    if (n_) lifeb200::Check(lifeb200_memcpy_h2d(ctx_, d_, batch.data(), n_ * 512), "Upload");
+  }
+  void Soups(uint64_t first_id, size_t n, uint64_t seed, int dist = 0) {
+    Reserve(n);
+    n_ = n;
+    lifeb200::Check(lifeb200_soup_dev(ctx_, static_cast<uint64_t*>(d_), first_id, n, seed, dist), "Soups");
+  }
+  void Step(unsigned gens) {
+    lifeb200::Check(lifeb200_step_batch_dev(ctx_, static_cast<uint64_t*>(d_), static_cast<uint64_t*>(d_), n_, gens), "Step");
+  }
+  std::vector<LifeState> Download() {
+    std::vector<LifeState> out(n_);
+    if (n_) lifeb200::Check(lifeb200_memcpy_d2h(ctx_, out.data(), d_, n_ * 512), "Download");
+    lifeb200::Check(lifeb200_sync(ctx_), "sync");
+    return out;
+  }
+  size_t size() const { return n_; }
+
+  // catalyst x projectile collision enumeration with fused Contains(LifeTarget(catalyst)) and
+  // stabilisation match; hits sorted by placement id
+  static std::vector<LifeHit> EnumerateCollisions(const std::vector<LifeState>& catalysts,
+                                                  const std::vector<LifeState>& projectiles, unsigned gens,
+                                                  unsigned stable_interval, uint64_t* n_skipped = nullptr,
+                                                  lifeb200_ctx* ctx = nullptr) {
+    ctx = ctx ? ctx : lifeb200::DefaultContext();
+    const uint64_t total = (uint64_t)catalysts.size() * projectiles.size() * 4096ull;
+    std::vector<LifeHit> hits(4096);
+    for (;;) {
+      uint64_t nh = 0, ns = 0;
+      int rc = lifeb200_enumerate_collisions(ctx, catalysts[0].state, (unsigned)catalysts.size(), projectiles[0].state,
+                                             (unsigned)projectiles.size(), 0, total, gens, stable_interval,
+                                             reinterpret_cast<lifeb200_hit*>(hits.data()), hits.size(), &nh, &ns);
+      if (rc == LIFEB200_E_OVERFLOW) { hits.resize(nh); continue; }
+      lifeb200::Check(rc, "EnumerateCollisions");
+      hits.resize(nh);
+      if (n_skipped) *n_skipped = ns;
+      return hits;
+    }
+  }
+
+ private:
+  void Reserve(size_t n) {
+    if (n <= cap_) return;
+    if (d_) lifeb200::Check(lifeb200_free(ctx_, d_), "free");
+    d_ = nullptr;
+    lifeb200::Check(lifeb200_malloc(ctx_, &d_, n * 512), "malloc");
+    cap_ = n;
+  }
+  lifeb200_ctx* ctx_;
+  void* d_ = nullptr;
+  size_t n_ = 0, cap_ = 0;
+};

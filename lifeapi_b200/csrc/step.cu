@@ -98,7 +98,10 @@ static inline unsigned grid_for(size_t n, int lpp) {
 
 int launch_step(lifeb200_ctx* ctx, cudaStream_t st, const uint64_t* in, uint64_t* out, size_t n, unsigned gens) {
   if (n == 0) return LIFEB200_OK;
-  int lpp = effective_lpp(ctx);
+  // Measured on B200 (profiles/r01_*): 4 lanes per pattern (16 words per lane) keeps the ALU pipe
+  // busiest when many generations run per launch; with few generations the launch is HBM-bound and
+  // 16 lanes per pattern (32 contiguous bytes per lane) coalesces best.
+  int lpp = ctx->lpp ? ctx->lpp : (gens >= 8 ? 4 : 16);
   LIFEB200_DISPATCH_LPP(lpp, (step_kernel<LPP><<<grid_for(n, LPP), kBlock, 0, st>>>(in, out, n, gens)));
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;

@@ -1,0 +1,119 @@
+// step_alt_test.cpp -- the reference's tests/StepAltTest.cpp:5-13 pattern (randomised differential,
+// bit-exact ==) written against the drop-in header include/LifeAPI_b200.hpp.  Where the reference
+// compares Step() with StepAlt(), this compares the B200 Step() with the oracle (oracle/ C port,
+// linked here as the checker) -- same call sites, same EXPECT_EQ discipline, no gtest needed.
+//
+// Build (tests/test_cpp_header.py does this):
+//   g++ -std=c++20 -O2 -Iinclude tests/cpp/step_alt_test.cpp -o step_alt_test
+//       lifeapi_b200/_lib/liblifeapi_b200.so oracle/_build/liblifeoracle.so
+#include <cstdio>
+#include <random>
+#include <vector>
+
+#include "LifeAPI_b200.hpp"
+
+extern "C" {
+void lo_step(uint64_t* s);
+void lo_step_alt(uint64_t* s);
+void lo_step_n(uint64_t* s, unsigned gens);
+void lo_neighbour_count(const uint64_t* s, uint64_t* planes);
+int lo_contains_target(const uint64_t* s, const uint64_t* target);
+}
+
+static int failures = 0;
+#define EXPECT_TRUE(c)                                                      \
+  do {                                                                      \
+    if (!(c)) { std::printf("FAIL %s:%d: %s\n", __FILE__, __LINE__, #c); failures++; } \
+  } while (0)
+#define EXPECT_EQ(a, b) EXPECT_TRUE((a) == (b))
+
+// Seeded stand-in for LifeState::RandomState (LifeAPI.hpp:63-69): rows uniform in [2^61, 2^62].
+static LifeState RandomState(std::mt19937_64& rng) {
+  std::uniform_int_distribution<uint64_t> dist(1ULL << 61, 1ULL << 62);
+  LifeState s;
+  for (int i = 0; i < N; i++) s[i] = dist(rng);
+  return s;
+}
+
+static void StepAltTest_Random() {
+  std::mt19937_64 rng(20240611);
+  const unsigned numIters = 10000;
+  for (unsigned i = 0; i < numIters; i++) {
+    LifeState a = RandomState(rng);
+    LifeState b = a;
+    a.Step();
+    b.StepAlt();
+    EXPECT_EQ(a, b);
+    if (i < 2000) {
+      LifeState c = RandomState(rng);
+      LifeState want = c;
+      lo_step(want.state);
+      LifeState want_alt = c;
+      lo_step_alt(want_alt.state);
+      c.Step();
+      EXPECT_EQ(c, want);
+      EXPECT_EQ(c, want_alt);
+    }
+  }
+}
+
+static void StepN_RPentomino() {
+  LifeState rp = LifeState::Parse("b2o$2o$bo!");
+  EXPECT_EQ(rp.GetPop(), 5u);
+  LifeState gpu = rp, cpu = rp;
+  for (unsigned g = 1; g <= 1000; g++) {
+    gpu.Step();
+    lo_step(cpu.state);
+    EXPECT_EQ(gpu, cpu);
+  }
+  EXPECT_EQ(gpu.GetPop(), 113u);                  // SURVEY.md 8c known answer
+  EXPECT_EQ(rp.Stepped(1000), gpu);               // Step(n) == n x Step()
+  EXPECT_EQ(rp.Stepped(100).GetPop(), 121u);
+  EXPECT_EQ(rp.Stepped(0), rp);
+}
+
+static void Batch_MatchesSingles() {
+  std::mt19937_64 rng(7);
+  std::vector<LifeState> batch(1000);
+  for (auto& s : batch) s = RandomState(rng);
+  std::vector<LifeState> want = batch;
+  for (auto& s : want) lo_step_n(s.state, 64);
+  std::vector<LifeState> host = batch;
+  LifeBatch::Step(host, 64);
+  EXPECT_TRUE(host == want);
+  LifeBatch resident;
+  resident.Upload(batch);
+  resident.Step(32);
+  resident.Step(32);
+  EXPECT_TRUE(resident.Download() == want);
+}
+
+static void NeighbourCount_And_Target() {
+  std::mt19937_64 rng(99);
+  for (int it = 0; it < 50; it++) {
+    LifeState s = RandomState(rng);
+    NeighbourCount nc(s);
+    uint64_t planes[4 * N];
+    lo_neighbour_count(s.state, planes);
+    EXPECT_TRUE(std::memcmp(&nc, planes, sizeof planes) == 0);
+    // Subtract(o) = Add(~o, ones): nc - nc == 0 on every plane (NeighbourCount.hpp:85-91)
+    NeighbourCount z = nc - nc;
+    EXPECT_TRUE(z.bit0.IsEmpty() && z.bit1.IsEmpty() && z.bit2.IsEmpty() && z.bit3.IsEmpty());
+    LifeState all;
+    for (unsigned n = 0; n <= 9; n++) all |= nc.WithExactly(n);
+    EXPECT_EQ(all, ~LifeState());
+    LifeTarget t(s & s.Moved(1, 0));
+    EXPECT_TRUE((s & s.Moved(1, 0)).Contains(t));
+    EXPECT_EQ(s.Contains(t), (bool)lo_contains_target(s.state, reinterpret_cast<const uint64_t*>(&t)));
+  }
+}
+
+int main() {
+  StepAltTest_Random();
+  StepN_RPentomino();
+  Batch_MatchesSingles();
+  NeighbourCount_And_Target();
+  if (failures) { std::printf("%d FAILURES\n", failures); return 1; }
+  std::printf("step_alt_test: all passed\n");
+  return 0;
+}
