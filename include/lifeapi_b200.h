@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define LIFEB200_ABI_VERSION 1
+#define LIFEB200_ABI_VERSION 2
 #define LIFEB200_WORDS 64          /* LifeAPI.hpp:12  const int N = 64 */
 #define LIFEB200_PATTERN_BYTES 512 /* sizeof(LifeState) */
 
@@ -132,6 +132,57 @@ int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_
 /* The same 64-bit fold of a resident batch: XOR over patterns of fold(p). */
 int lifeb200_fold_dev(lifeb200_ctx* ctx, const uint64_t* patterns, size_t n, uint64_t first_id,
                       uint64_t* pop_sum, uint64_t* hash_xor);
+
+/* ---- A9  three-valued step through bitslicing/unknown_step.hpp --------------------------
+ * The reference ships the generated cover without a consumer; the loop is the one
+ * LifeStable.hpp:429-469 uses for stable_simple.hpp: on = NeighbourCount(state), unk =
+ * NeighbourCount(unknown) (3x3 sums INCLUDING the centre), per word the cover maps
+ * (current_unknown, current_on, on2..on0, unk3..unk0) -> (naive_next_unknown, naive_next_on).
+ * state / unknown are separate plane arrays of n x 512 B; out may alias in.  gens may be 0. */
+int lifeb200_unknown_step_batch_dev(lifeb200_ctx* ctx, const uint64_t* state_in, const uint64_t* unknown_in,
+                                    uint64_t* state_out, uint64_t* unknown_out, size_t n, unsigned gens);
+int lifeb200_unknown_step_batch_host(lifeb200_ctx* ctx, const uint64_t* state_in, const uint64_t* unknown_in,
+                                     uint64_t* state_out, uint64_t* unknown_out, size_t n, unsigned gens);
+
+/* ---- LifeHistory (LifeHistory.hpp:8-12): record = state, history, marked, original = 2048 B.
+ * The reference has no stepping member; the build-defined step is, `gens` times,
+ * state.Step() (LifeAPI.hpp:1196-1216) then history |= state (:255-260).  In place. */
+int lifeb200_history_step_batch_dev(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens);
+
+/* ---- A10  LifeStable full-grid passes (LifeStable.hpp:366-729) ---------------------------
+ * record = the 10 member planes in declaration order state, unknown, live2, live3, dead0, dead1,
+ * dead2, dead4, dead5, dead6 (LifeStable.hpp:39-53) = 640 words = 5120 B == sizeof(LifeStable).
+ * Records are updated in place exactly as the reference member leaves *this (including what has
+ * already been written when a pass reports an inconsistency); flags[i] (may be NULL) receives
+ * PropagateResult (LifeStable.hpp:123-126) as CONSISTENT | CHANGED bits. */
+#define LIFEB200_STABLE_WORDS 640
+#define LIFEB200_STABLE_BYTES 5120
+enum {
+  LIFEB200_STABLE_PROPAGATE_SIMPLE_STEP = 0, /* LifeStable.hpp:414-503 + stable_simple.hpp */
+  LIFEB200_STABLE_SYNCHRONISE = 1,           /* SynchroniseStateKnown :526-556 */
+  LIFEB200_STABLE_UPDATE_OPTIONS = 2,        /* :558-615 + stable_count.hpp */
+  LIFEB200_STABLE_SIGNAL_NEIGHBOURS = 3,     /* :617-675 + stable_signal.hpp */
+  LIFEB200_STABLE_PROPAGATE_STEP = 4,        /* :695-716 */
+  LIFEB200_STABLE_PROPAGATE = 5,             /* :718-729, to the fixed point */
+  LIFEB200_STABLE_STABILISE_OPTIONS = 6,     /* :677-693 */
+  LIFEB200_STABLE_PROPAGATE_SIMPLE = 7       /* :505-524 */
+};
+#define LIFEB200_STABLE_CONSISTENT 1u
+#define LIFEB200_STABLE_CHANGED 2u
+int lifeb200_stable_pass_dev(lifeb200_ctx* ctx, uint64_t* records, size_t n, int pass, uint8_t* flags);
+int lifeb200_stable_pass_host(lifeb200_ctx* ctx, uint64_t* records, size_t n, int pass, uint8_t* flags);
+/* LifeStable::Vulnerable() (LifeStable.hpp:366-412 + stable_vulnerable.hpp): out = n x 512 B. */
+int lifeb200_stable_vulnerable_dev(lifeb200_ctx* ctx, const uint64_t* records, uint64_t* out, size_t n);
+
+/* ---- A9b  refined three-valued step (bitslicing/unknown_step_refined_m.hpp, variant 0; the
+ * older unknown_step_refined.hpp cover, variant 1).  No consumer in the reference; inputs follow
+ * the generator (unknown_step_refined.py:93-118): option planes l2..d6 of the stable record,
+ * s2..s0 = NeighbourCount(stable.state), live = NeighbourCount(current_on), m3..m0 =
+ * NeighbourCount::Subtract(s, live) (NeighbourCount.hpp:85-91), on2..on0 = live for variant 1.
+ * Outputs: three planes of n x 512 B each. */
+int lifeb200_unknown_step_refined_dev(lifeb200_ctx* ctx, const uint64_t* records, const uint64_t* current_on,
+                                      const uint64_t* current_unknown, size_t n, int variant, uint64_t* next_on,
+                                      uint64_t* next_unknown, uint64_t* next_unknown_stable);
 
 /* ---- roofline denominator: measured LOP3 lane-instructions per second ------------------- */
 int lifeb200_measure_int_peak(lifeb200_ctx* ctx, double* lop3_lane_instr_per_s, double* sm_mhz_effective);

@@ -22,6 +22,12 @@ PATTERN_BYTES = 512
 
 E_OK, E_CUDA, E_ARG, E_OVERFLOW, E_NODEVICE = 0, 1, 2, 3, 4
 
+STABLE_WORDS = 640
+STABLE_BYTES = 5120
+(STABLE_PROPAGATE_SIMPLE_STEP, STABLE_SYNCHRONISE, STABLE_UPDATE_OPTIONS, STABLE_SIGNAL_NEIGHBOURS, STABLE_PROPAGATE_STEP,
+ STABLE_PROPAGATE, STABLE_STABILISE_OPTIONS, STABLE_PROPAGATE_SIMPLE) = range(8)
+STABLE_CONSISTENT, STABLE_CHANGED = 1, 2
+
 
 class LifeB200Error(RuntimeError):
     def __init__(self, code: int, msg: str):
@@ -72,6 +78,13 @@ SIGNATURES = {
     "lifeb200_soup_survey": (C.c_int, [_vp, C.c_uint64, C.c_size_t, C.c_uint64, C.c_int, C.c_uint, _vp, C.c_size_t,
                                        _u64p, _u64p, _u64p]),
     "lifeb200_fold_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_uint64, _u64p, _u64p]),
+    "lifeb200_unknown_step_batch_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_size_t, C.c_uint]),
+    "lifeb200_unknown_step_batch_host": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_size_t, C.c_uint]),
+    "lifeb200_history_step_batch_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_uint]),
+    "lifeb200_stable_pass_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_int, _vp]),
+    "lifeb200_stable_pass_host": (C.c_int, [_vp, _vp, C.c_size_t, C.c_int, _vp]),
+    "lifeb200_stable_vulnerable_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_unknown_step_refined_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp, _vp]),
     "lifeb200_measure_int_peak": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 }
 
@@ -295,3 +308,82 @@ class Engine:
         ps, hx = C.c_uint64(), C.c_uint64()
         self._check(self.lib.lifeb200_fold_dev(self._h, _ptr(d_patterns), n, first_id, C.byref(ps), C.byref(hx)))
         return ps.value, hx.value
+
+    # -- generated circuits: three-valued step, LifeHistory, LifeStable passes -----------------------
+    def unknown_step_batch_dev(self, d_state_in, d_unknown_in, d_state_out, d_unknown_out, n: int, gens: int) -> None:
+        self._check(self.lib.lifeb200_unknown_step_batch_dev(self._h, _ptr(d_state_in), _ptr(d_unknown_in), _ptr(d_state_out),
+                                                             _ptr(d_unknown_out), n, gens))
+
+    def unknown_step_batch_host(self, state: np.ndarray, unknown: np.ndarray, gens: int):
+        state = np.ascontiguousarray(state, dtype=np.uint64)
+        unknown = np.ascontiguousarray(unknown, dtype=np.uint64)
+        if state.shape != unknown.shape:
+            raise ValueError("state / unknown shapes differ")
+        so, uo = np.empty_like(state), np.empty_like(unknown)
+        self._check(self.lib.lifeb200_unknown_step_batch_host(self._h, _ptr(state), _ptr(unknown), _ptr(so), _ptr(uo),
+                                                              state.size // WORDS, gens))
+        return so, uo
+
+    def history_step_batch_dev(self, d_records, n: int, gens: int) -> None:
+        self._check(self.lib.lifeb200_history_step_batch_dev(self._h, _ptr(d_records), n, gens))
+
+    def history_step_batch(self, records: np.ndarray, gens: int) -> np.ndarray:
+        """Convenience: (n, 4, 64) LifeHistory records, host in / host out via the *_dev entry point."""
+        records = np.ascontiguousarray(records, dtype=np.uint64)
+        n = records.size // (4 * WORDS)
+        out = np.empty_like(records)
+        d = self.malloc(max(records.nbytes, 16))
+        try:
+            self.h2d(d, records)
+            self.history_step_batch_dev(d, n, gens)
+            self.d2h(out, d)
+            self.sync()
+        finally:
+            self.free(d)
+        return out
+
+    def stable_pass_dev(self, d_records, n: int, which: int, d_flags=None) -> None:
+        self._check(self.lib.lifeb200_stable_pass_dev(self._h, _ptr(d_records), n, which, _ptr(d_flags)))
+
+    def stable_pass_host(self, records: np.ndarray, which: int):
+        """(n, 10, 64) LifeStable records -> (updated records, flags uint8)."""
+        rec = np.ascontiguousarray(records, dtype=np.uint64).copy()
+        n = rec.size // STABLE_WORDS
+        flags = np.zeros(n, dtype=np.uint8)
+        self._check(self.lib.lifeb200_stable_pass_host(self._h, _ptr(rec), n, which, _ptr(flags)))
+        return rec, flags
+
+    def stable_vulnerable(self, records: np.ndarray) -> np.ndarray:
+        records = np.ascontiguousarray(records, dtype=np.uint64)
+        n = records.size // STABLE_WORDS
+        out = np.empty((n, WORDS), dtype=np.uint64)
+        d, do = self.malloc(max(records.nbytes, 16)), self.malloc(max(out.nbytes, 16))
+        try:
+            self.h2d(d, records)
+            self._check(self.lib.lifeb200_stable_vulnerable_dev(self._h, d, do, n))
+            self.d2h(out, do)
+            self.sync()
+        finally:
+            self.free(d)
+            self.free(do)
+        return out
+
+    def unknown_step_refined(self, records: np.ndarray, current_on: np.ndarray, current_unknown: np.ndarray, variant: int = 0):
+        records = np.ascontiguousarray(records, dtype=np.uint64)
+        current_on = np.ascontiguousarray(current_on, dtype=np.uint64)
+        current_unknown = np.ascontiguousarray(current_unknown, dtype=np.uint64)
+        n = records.size // STABLE_WORDS
+        outs = [np.empty((n, WORDS), dtype=np.uint64) for _ in range(3)]
+        bufs = [self.malloc(max(a.nbytes, 16)) for a in (records, current_on, current_unknown, *outs)]
+        try:
+            for b, a in zip(bufs[:3], (records, current_on, current_unknown)):
+                self.h2d(b, a)
+            self._check(self.lib.lifeb200_unknown_step_refined_dev(self._h, bufs[0], bufs[1], bufs[2], n, variant, bufs[3],
+                                                                   bufs[4], bufs[5]))
+            for b, a in zip(bufs[3:], outs):
+                self.d2h(a, b)
+            self.sync()
+        finally:
+            for b in bufs:
+                self.free(b)
+        return tuple(outs)

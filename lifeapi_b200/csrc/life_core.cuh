@@ -8,7 +8,7 @@
 // are exchanged with __shfl_sync whose width=LPP argument gives the torus wrap.
 //
 // The rule is LifeState::StepAlt (LifeAPI.hpp:1218-1254) restated as 3-input LUTs:
-//   per 32-cell half-word and generation: 2 SHF + 10 LOP3.
+//   per 32-cell half-word and generation: 2 SHF + 9 LOP3 (SURVEY.md 8d counts 2 + 10 for the literal form).
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -50,18 +50,22 @@ __device__ __forceinline__ Cnt count_rows(uint32_t lo, uint32_t hi) {
   return c;
 }
 
-// StepAlt tail (LifeAPI.hpp:1236-1252): two full adders over the three column counts, carry
-// fix-up and the B3/S23 select.  8 LOP3 per half-word.
+// B3/S23 select over the three column counts (the job of the StepAlt tail, LifeAPI.hpp:1236-1252).
+// X = u0+c0+d0 and Y = u1+c1+d1 are each encoded in two LUTs -- X as (not-all-equal, majority),
+// a Gray code of 0..3, Y as (parity, majority) -- and next = [X+2Y == 3] | a & [X+2Y == 4] is then
+// three more LUTs found by exhaustive search (tools/lut_search.c) and checked on all 2^7 inputs
+// (tests/test_oracle.py::test_rule_luts_exhaustive).  7 LOP3 per half-word instead of the 8 of the
+// literal two-full-adder form.
+constexpr int kNotAllEq = 0x7E;  // !(a==b==c)
 __device__ __forceinline__ uint32_t rule32(uint32_t a, uint32_t u0, uint32_t u1, uint32_t c0, uint32_t c1,
                                            uint32_t d0, uint32_t d1) {
-  uint32_t fs = lop3<kXor3>(u0, c0, d0);
-  uint32_t fc = lop3<kMaj>(u0, c0, d0);
-  uint32_t cs = lop3<kXor3>(u1, c1, d1);
-  uint32_t cc = lop3<kMaj>(u1, c1, d1);
-  cc = lop3<kXorAnd>(cc, fc, cs);
-  uint32_t y = lop3<kXor3>(fc, cs, cc);
-  uint32_t t = lop3<kXorThenAnd>(fs, cc, y);
-  return lop3<kAndOr>(t, a, fs);
+  uint32_t xa = lop3<kNotAllEq>(u0, c0, d0);
+  uint32_t xb = lop3<kMaj>(u0, c0, d0);
+  uint32_t ya = lop3<kXor3>(u1, c1, d1);
+  uint32_t yb = lop3<kMaj>(u1, c1, d1);
+  uint32_t g1 = lop3<0x16>(xb, xa, a);
+  uint32_t g2 = lop3<0x6D>(g1, yb, a);
+  return lop3<0x09>(g2, ya, xa);
 }
 
 template <int LPP>
@@ -213,6 +217,52 @@ __device__ __forceinline__ uint64_t soup_word(uint64_t seed, uint64_t id, int i,
   uint64_t r = splitmix64(seed + id * 64 + (uint64_t)i);
   if (dist == 1) r = (1ULL << 61) + (r % ((1ULL << 61) + 1));  // shape of LifeAPI.hpp:21-22
   return r;
+}
+
+}  // namespace lifeb200
+
+namespace lifeb200 {
+
+// flat view of a tile's 2*W registers (k < W: low halves, else high halves); indices are
+// compile-time after unrolling, so everything stays in registers
+template <int LPP>
+__device__ __forceinline__ uint32_t& reg(Tile<LPP>& t, int k) {
+  return k < Tile<LPP>::W ? t.lo[k] : t.hi[k - Tile<LPP>::W];
+}
+template <int LPP>
+__device__ __forceinline__ uint32_t reg(const Tile<LPP>& t, int k) {
+  return k < Tile<LPP>::W ? t.lo[k] : t.hi[k - Tile<LPP>::W];
+}
+
+// 3x3 dilation of a plane on the torus: ZOI (LifeAPI.hpp:521-536) or, with hollow = true,
+// ZOIHollow (LifeAPI.hpp:541-562, the centre cell itself is left out).
+template <int LPP>
+__device__ __forceinline__ Tile<LPP> dilate(const Tile<LPP>& t, int sub, bool hollow) {
+  constexpr int W = Tile<LPP>::W;
+  Tile<LPP> mid, full, out;
+#pragma unroll
+  for (int w = 0; w < W; w++) {
+    uint32_t lo = t.lo[w], hi = t.hi[w];
+    uint32_t l_lo = __funnelshift_l(hi, lo, 1), l_hi = __funnelshift_l(lo, hi, 1);
+    uint32_t r_lo = __funnelshift_r(lo, hi, 1), r_hi = __funnelshift_r(hi, lo, 1);
+    mid.lo[w] = l_lo | r_lo; mid.hi[w] = l_hi | r_hi;
+    full.lo[w] = mid.lo[w] | lo; full.hi[w] = mid.hi[w] | hi;
+  }
+  uint32_t up_lo = full.lo[W - 1], up_hi = full.hi[W - 1], dn_lo = full.lo[0], dn_hi = full.hi[0];
+  if constexpr (LPP > 1) {
+    up_lo = __shfl_sync(0xffffffffu, up_lo, sub + LPP - 1, LPP);
+    up_hi = __shfl_sync(0xffffffffu, up_hi, sub + LPP - 1, LPP);
+    dn_lo = __shfl_sync(0xffffffffu, dn_lo, sub + 1, LPP);
+    dn_hi = __shfl_sync(0xffffffffu, dn_hi, sub + 1, LPP);
+  }
+#pragma unroll
+  for (int w = 0; w < W; w++) {
+    uint32_t a_lo = w == 0 ? up_lo : full.lo[w - 1], a_hi = w == 0 ? up_hi : full.hi[w - 1];
+    uint32_t b_lo = w == W - 1 ? dn_lo : full.lo[w + 1], b_hi = w == W - 1 ? dn_hi : full.hi[w + 1];
+    out.lo[w] = lop3<kOr3>(a_lo, hollow ? mid.lo[w] : full.lo[w], b_lo);
+    out.hi[w] = lop3<kOr3>(a_hi, hollow ? mid.hi[w] : full.hi[w], b_hi);
+  }
+  return out;
 }
 
 }  // namespace lifeb200

@@ -35,7 +35,7 @@ def aligned_copy(a: np.ndarray, align: int = 64) -> np.ndarray:
 
 
 def build_port(force: bool = False) -> str:
-    srcs = [os.path.join(HERE, "life_oracle.c"), os.path.join(HERE, "circuits_oracle.c")]
+    srcs = [os.path.join(HERE, f) for f in ("life_oracle.c", "circuits_oracle.c", "stable_oracle.c", "circuit_tables.h")]
     if force or not os.path.exists(PORT_SO) or any(os.path.getmtime(s) > os.path.getmtime(PORT_SO) for s in srcs):
         subprocess.run(["make", "-C", HERE, "port"], check=True, stdout=subprocess.DEVNULL)
     return PORT_SO
@@ -113,6 +113,13 @@ class Port:
                                                _u64p, _u32p, _u32p, C.c_size_t, C.POINTER(C.c_uint64)])
         _sig(lib, "lo_survey", C.c_size_t, [C.c_uint64, C.c_size_t, C.c_uint64, C.c_int, C.c_uint, _u64p, _u32p, C.c_size_t,
                                             C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)])
+        _sig(lib, "lo_circuit_eval", C.c_int, [C.c_int, _u64p, _u64p])
+        _sig(lib, "lo_zoi_hollow", None, [_u64p, _u64p])
+        _sig(lib, "lo_unknown_step_sop_batch", None, [_u64p, _u64p, C.c_size_t, C.c_uint, C.c_int])
+        _sig(lib, "lo_stable_pass", C.c_uint, [_u64p, C.c_int])
+        _sig(lib, "lo_stable_pass_batch", None, [_u64p, C.c_size_t, C.c_int, _u8p, C.c_int])
+        _sig(lib, "lo_stable_vulnerable", None, [_u64p, _u64p])
+        _sig(lib, "lo_refined_step", None, [_u64p, _u64p, _u64p, C.c_int, _u64p, _u64p, _u64p])
 
     # -- helpers returning fresh arrays ---------------------------------------------------------
     def threads(self) -> int:
@@ -191,6 +198,48 @@ class Port:
         nh = min(nh, cap)
         return ids[:nh], ff[:nh], rec[:nh], ns.value
 
+    def circuit_eval(self, which: int, inputs: np.ndarray) -> np.ndarray:
+        """inputs: (n_in,) uint64 words -> (n_out,) uint64 words through the cube table of fragment `which`."""
+        out = np.zeros(16, dtype=np.uint64)
+        k = self.lib.lo_circuit_eval(which, np.ascontiguousarray(inputs, dtype=np.uint64), out)
+        if k < 0:
+            raise ValueError(which)
+        return out[:k]
+
+    def zoi_hollow(self, s):
+        out = np.empty(64, dtype=np.uint64)
+        self.lib.lo_zoi_hollow(np.ascontiguousarray(s, dtype=np.uint64), out)
+        return out
+
+    def unknown_step_sop_batch(self, state, unknown, gens, threads: int = 0):
+        s = np.ascontiguousarray(state, dtype=np.uint64).copy()
+        u = np.ascontiguousarray(unknown, dtype=np.uint64).copy()
+        self.lib.lo_unknown_step_sop_batch(s.reshape(-1), u.reshape(-1), s.size // 64, gens, threads)
+        return s, u
+
+    def stable_pass_batch(self, planes, which: int, threads: int = 0, fn="lo_stable_pass_batch", lib=None):
+        """planes: (n, 10, 64) uint64 LifeStable records -> (new planes, flags uint8: bit0 consistent, bit1 changed)."""
+        p = aligned_copy(np.asarray(planes, dtype=np.uint64).reshape(-1, 10, 64))
+        flags = np.zeros(p.shape[0], dtype=np.uint8)
+        getattr(lib or self.lib, fn)(p.reshape(-1), p.shape[0], which, flags, threads)
+        return p, flags
+
+    def stable_vulnerable(self, planes, fn="lo_stable_vulnerable", lib=None):
+        p = aligned_copy(np.asarray(planes, dtype=np.uint64).reshape(-1, 10, 64))
+        out = np.empty((p.shape[0], 64), dtype=np.uint64)
+        for i in range(p.shape[0]):
+            getattr(lib or self.lib, fn)(p[i].reshape(-1), out[i])
+        return out
+
+    def refined_step(self, planes, cur_on, cur_unk, variant: int, fn="lo_refined_step", lib=None):
+        p = aligned_copy(np.asarray(planes, dtype=np.uint64).reshape(-1, 10, 64))
+        con = aligned_copy(np.asarray(cur_on, dtype=np.uint64).reshape(-1, 64))
+        cun = aligned_copy(np.asarray(cur_unk, dtype=np.uint64).reshape(-1, 64))
+        outs = [np.empty_like(con) for _ in range(3)]
+        for i in range(p.shape[0]):
+            getattr(lib or self.lib, fn)(p[i].reshape(-1), con[i], cun[i], variant, outs[0][i], outs[1][i], outs[2][i])
+        return tuple(outs)
+
     def survey(self, first_id, n, seed, dist, gens, cap):
         ids = np.zeros(max(cap, 1), dtype=np.uint64)
         pops = np.zeros(max(cap, 1), dtype=np.uint32)
@@ -239,6 +288,11 @@ class Ref:
         _sig(lib, "ref_enumerate", C.c_size_t, [_u64p, C.c_uint, _u64p, C.c_uint, C.c_uint64, C.c_uint64, C.c_uint, C.c_uint,
                                                 _u64p, _u32p, _u32p, C.c_size_t, C.POINTER(C.c_uint64)])
         _sig(lib, "ref_survey_states", None, [_u64p, C.c_size_t, C.c_uint, _u8p, _u32p])
+        _sig(lib, "ref_stable_pass", C.c_uint, [_u64p, C.c_int])
+        _sig(lib, "ref_stable_pass_batch", None, [_u64p, C.c_size_t, C.c_int, _u8p, C.c_int])
+        _sig(lib, "ref_stable_vulnerable", None, [_u64p, _u64p])
+        _sig(lib, "ref_zoi_hollow", None, [_u64p, _u64p])
+        _sig(lib, "ref_refined_step", None, [_u64p, _u64p, _u64p, C.c_int, _u64p, _u64p, _u64p])
 
     def isa(self) -> str:
         return self.lib.ref_isa().decode()
@@ -307,6 +361,20 @@ class Ref:
     def enumerate(self, catalysts, projectiles, id_begin, id_end, gens, stable_interval, cap):
         return Port.enumerate(self, catalysts, projectiles, id_begin, id_end, gens, stable_interval, cap,
                               fn="ref_enumerate", lib=self.lib)
+
+    def stable_pass_batch(self, planes, which: int, threads: int = 0):
+        return Port.stable_pass_batch(self, planes, which, threads, fn="ref_stable_pass_batch", lib=self.lib)
+
+    def stable_vulnerable(self, planes):
+        return Port.stable_vulnerable(self, planes, fn="ref_stable_vulnerable", lib=self.lib)
+
+    def refined_step(self, planes, cur_on, cur_unk, variant: int):
+        return Port.refined_step(self, planes, cur_on, cur_unk, variant, fn="ref_refined_step", lib=self.lib)
+
+    def zoi_hollow(self, s):
+        out = np.empty(64, dtype=np.uint64)
+        self.lib.ref_zoi_hollow(np.ascontiguousarray(s, dtype=np.uint64), out)
+        return out
 
     def survey_states(self, states, gens):
         st = np.ascontiguousarray(states, dtype=np.uint64).copy()

@@ -15,7 +15,9 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 from oracle.loader import Port, Ref, build_ref  # noqa: E402
+from stable_inputs import stable_records  # noqa: E402
 
 OUT = os.path.dirname(os.path.abspath(__file__))
 SEED = 0x4C696665415049
@@ -77,6 +79,15 @@ def glider_variants(ref: Ref) -> np.ndarray:
             out.append(s.copy())
             s = ref.step(s)
     return np.stack(out)
+
+
+def unknown_free_noise(rng, n: int) -> np.ndarray:
+    """A few random live cells per pattern (perturbs the still-life field so live != stable counts)."""
+    out = np.zeros((n, 64), dtype=np.uint64)
+    for p in range(n):
+        for _ in range(6):
+            out[p, int(rng.integers(64))] |= np.uint64(1) << np.uint64(int(rng.integers(64)))
+    return out
 
 
 def main() -> None:
@@ -160,6 +171,28 @@ def main() -> None:
     res = [ref.unknown_step_batch(state, unk, k, 1) for k in g3]
     np.savez_compressed(os.path.join(OUT, "unknown_step.npz"), state=state, unknown=unk, gens=np.array(g3),
                         next_state=np.stack([r[0] for r in res]), next_unknown=np.stack([r[1] for r in res]))
+
+    # ---- LifeStable passes, Vulnerable, refined steps (reference LifeStable.hpp members) -------
+    clean = stable_records(10, 2024)
+    dirty = rng.integers(0, 1 << 63, size=(6, 10, 64), dtype=np.uint64) << np.uint64(1)
+    dirty[3:, 2:] &= rng.integers(0, 1 << 63, size=(3, 8, 64), dtype=np.uint64) & rng.integers(0, 1 << 63, size=(3, 8, 64), dtype=np.uint64)
+    dirty[3:, 0] &= ~dirty[3:, 1]
+    recs = np.concatenate([clean, dirty])
+    outs, flags = [], []
+    for which in range(8):
+        o, f = ref.stable_pass_batch(recs, which, 1)
+        outs.append(o)
+        flags.append(f)
+    propagated, _ = ref.stable_pass_batch(recs, 5, 1)
+    vuln = ref.stable_vulnerable(np.concatenate([recs, propagated]))
+    cur_on = np.concatenate([clean[:, 0], rng.integers(0, 1 << 63, size=(6, 64), dtype=np.uint64)])
+    cur_on[:10] = ref.step_batch(cur_on[:10] | unknown_free_noise(rng, 10), 1, 1)
+    cur_unk = recs[:, 1].copy()
+    refined = [np.stack(ref.refined_step(propagated, cur_on, cur_unk, v)) for v in (0, 1)]
+    np.savez_compressed(os.path.join(OUT, "stable.npz"), records=recs, passes=np.stack(outs), flags=np.stack(flags),
+                        vulnerable_in=np.concatenate([recs, propagated]), vulnerable=vuln, refined_records=propagated,
+                        refined_on=cur_on, refined_unknown=cur_unk, refined_m=refined[0], refined_old=refined[1])
+    print("stable flags per pass:", [np.bincount(f, minlength=4).tolist() for f in flags])
 
     for f in sorted(os.listdir(OUT)):
         if f.endswith(".npz"):

@@ -172,3 +172,131 @@ def test_port_survey_matches_reference_predicates(port, ref):
     assert (pop[act.astype(bool)] == pops).all()
     assert int(pop.sum()) == ps
     assert port.fold_batch(final, 123) == (ps, hx)
+
+
+# ---- generated circuits: emitter, cube tables, LifeStable passes ------------------------------
+def _lop3(lut, a, b, c):
+    r = 0
+    for k in range(8):
+        if lut >> k & 1:
+            r |= (a if k & 4 else ~a) & (b if k & 2 else ~b) & (c if k & 1 else ~c)
+    return r & 1
+
+
+def test_rule_luts_exhaustive():
+    """The 7-LUT B3/S23 select in csrc/life_core.cuh (rule32) equals the rule on all 2^7 inputs."""
+    import os
+    import re
+    from conftest import ROOT
+    src = open(os.path.join(ROOT, "lifeapi_b200", "csrc", "life_core.cuh")).read()
+    body = src[src.index("uint32_t rule32("):]
+    body = body[:body.index("\n}\n")]
+    consts = {"kNotAllEq": 0x7E, "kMaj": 0xE8, "kXor3": 0x96}
+    luts = [consts.get(m, None) if not m.startswith("0x") else int(m, 16) for m in re.findall(r"lop3<(\w+)>", body)]
+    assert luts == [0x7E, 0xE8, 0x96, 0xE8, 0x16, 0x6D, 0x09]
+    for r in range(128):
+        a, u0, c0, d0, u1, c1, d1 = [(r >> i) & 1 for i in range(7)]
+        s = u0 + c0 + d0 + 2 * (u1 + c1 + d1)
+        xa, xb = _lop3(0x7E, u0, c0, d0), _lop3(0xE8, u0, c0, d0)
+        ya, yb = _lop3(0x96, u1, c1, d1), _lop3(0xE8, u1, c1, d1)
+        g1 = _lop3(0x16, xb, xa, a)
+        g2 = _lop3(0x6D, g1, yb, a)
+        assert _lop3(0x09, g2, ya, xa) == int(s == 3 or (a and s == 4))
+
+
+def test_emitted_circuits_equal_the_fragments_on_every_input():
+    """circuits.json -> LUT networks == SOP cubes on all 2^k inputs; generated files are in sync."""
+    import os
+    from conftest import ROOT
+    from lifeapi_b200.bitslicing import emit_cuda as E
+    items = E.load_json()
+    assert [c.name for c, _ in items] == list(E.CIRCUITS)
+    for c, net in items:
+        E.verify(c, net)
+        assert E.synthesize(c).to_json() == net.to_json()
+        assert c.inputs == E.CIRCUITS[c.name]["inputs"] and c.outputs == E.CIRCUITS[c.name]["outputs"]
+    assert E.render_cuda(items) == open(E.CUH_PATH).read()
+    from oracle import make_tables
+    assert make_tables.render_tables([c for c, _ in items]) == open(make_tables.TABLES_PATH).read()
+    ref_dir = "/root/reference/bitslicing"
+    if os.path.isdir(ref_dir):  # the committed cubes are exactly what the reference's text says
+        for c, _ in items:
+            spec = E.CIRCUITS[c.name]
+            parsed = E.parse_hpp(c.name, open(os.path.join(ref_dir, spec["file"])).read(), spec["inputs"], spec["outputs"],
+                                 f"bitslicing/{spec['file']}")
+            assert parsed.to_json() == c.to_json()
+
+
+def test_emitter_espresso_hook_round_trip():
+    from lifeapi_b200.bitslicing import emit_cuda as E
+    c = E.from_espresso("toy", ["1-0 10", "-11 11", "0-- 01"], "#.phase 10", ["a", "b", "c"], ["x", "y"])
+    assert c.inverted == [False, True] and len(c.terms) == 3
+    net = E.synthesize(c)
+    E.verify(c, net)
+    text = "x |= a & (~c);\n{ uint64_t temp = b & c; x |= temp; y |= temp; }\ny |= (~a);\ny = ~y;\n"
+    assert E.parse_hpp("toy", text, ["a", "b", "c"], ["x", "y"]).terms == c.terms
+
+
+def test_port_cube_tables_vs_json(port):
+    from lifeapi_b200.bitslicing import emit_cuda as E
+    rng = np.random.default_rng(5)
+    for which, (c, net) in enumerate(E.load_json()):
+        words = rng.integers(0, 1 << 63, size=len(c.inputs), dtype=np.uint64) << np.uint64(1) | rng.integers(0, 2, size=len(c.inputs), dtype=np.uint64)
+        got = port.circuit_eval(which, words)
+        full = (1 << 64) - 1
+        want = E.eval_net(net, [int(w) for w in words], full)
+        assert [int(g) for g in got] == want, c.name
+
+
+def test_port_stable_golden(port):
+    g = golden("stable.npz")
+    for which in range(8):
+        out, flags = port.stable_pass_batch(g["records"], which)
+        assert (out == g["passes"][which]).all(), which
+        assert (flags == g["flags"][which]).all(), which
+    assert (port.stable_vulnerable(g["vulnerable_in"]) == g["vulnerable"]).all()
+    for v, key in ((0, "refined_m"), (1, "refined_old")):
+        got = port.refined_step(g["refined_records"], g["refined_on"], g["refined_unknown"], v)
+        assert (np.stack(got) == g[key]).all()
+
+
+def test_port_unknown_step_sop_golden(port):
+    g = golden("unknown_step.npz")
+    for i, k in enumerate(g["gens"]):
+        s, u = port.unknown_step_sop_batch(g["state"], g["unknown"], int(k))
+        assert (s == g["next_state"][i]).all() and (u == g["next_unknown"][i]).all()
+
+
+def test_port_vs_reference_stable_passes(port, ref):
+    from stable_inputs import stable_records
+    rng = np.random.default_rng(99)
+    clean = stable_records(48, 31337)
+    dirty = rng.integers(0, 1 << 63, size=(16, 10, 64), dtype=np.uint64) << np.uint64(1)
+    recs = np.concatenate([clean, dirty])
+    cur = recs
+    for which in (1, 2, 3, 0, 4, 6, 7, 5, 5):  # chained: later passes see realistic intermediate records
+        a, fa = port.stable_pass_batch(cur, which)
+        b, fb = ref.stable_pass_batch(cur, which)
+        assert (a == b).all() and (fa == fb).all(), which
+        cur = b
+    assert (port.stable_vulnerable(cur) == ref.stable_vulnerable(cur)).all()
+    con = rng.integers(0, 1 << 63, size=(64, 64), dtype=np.uint64)
+    for v in (0, 1):
+        assert all((x == y).all() for x, y in zip(port.refined_step(cur, con, recs[:, 1], v), ref.refined_step(cur, con, recs[:, 1], v)))
+    for s in clean[:8, 0]:
+        assert (port.zoi_hollow(s) == ref.zoi_hollow(s)).all()
+
+
+def test_port_unknown_step_sop_vs_reference_and_semantics(port, ref):
+    from stable_inputs import three_valued_patterns
+    st, un = three_valued_patterns(64, 77, port.soup(5000, 64, SEED, 0), port.zoi)
+    a = port.unknown_step_sop_batch(st, un, 6)
+    b = ref.unknown_step_batch(st, un, 6)
+    c = port.unknown_step_batch(st, un, 6)  # per-cell semantic restatement (unknown_step.py:3-38)
+    assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
+    assert (a[0] == c[0]).all() and (a[1] == c[1]).all()
+    # overlapping state/unknown planes exercise the cover's don't-care rows: SOP port == reference text
+    rng = np.random.default_rng(4)
+    r = rng.integers(0, 1 << 63, size=(2, 32, 64), dtype=np.uint64)
+    a, b = port.unknown_step_sop_batch(r[0], r[1], 3), ref.unknown_step_batch(r[0], r[1], 3)
+    assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
