@@ -8,7 +8,7 @@
 // are exchanged with __shfl_sync whose width=LPP argument gives the torus wrap.
 //
 // The rule is LifeState::StepAlt (LifeAPI.hpp:1218-1254) restated as 3-input LUTs:
-//   per 32-cell half-word and generation: 2 SHF + 9 LOP3 (SURVEY.md 8d counts 2 + 10 for the literal form).
+//   per 32-cell half-word and generation: 2 SHF + 8 LOP3 (SURVEY.md 8d counts 2 + 10 for the literal form).
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -68,6 +68,30 @@ __device__ __forceinline__ uint32_t rule32(uint32_t a, uint32_t u0, uint32_t u1,
   return lop3<0x09>(g2, ya, xa);
 }
 
+// Pair-shared form of the same select, found by SAT-based exact synthesis (tools/lut_synth_pair_z3.py,
+// solution in tools/pair_0_4_4.solution.txt) and checked on all inputs in tests/test_oracle.py:
+// four LUTs turn the 2-bit counts (a, b) of two adjacent columns into a 3-signal code of a+b that is
+// shared by BOTH columns of the pair; four more give next = [a+b+c == 3] | cell & [a+b+c == 4] from
+// that code, the count c of the column on the far side and the centre cell.  8 + 4 = 12 LOP3 per two
+// half-words instead of 2 x 7.
+struct PairCode {
+  uint32_t p8, p9, p10;
+};
+__device__ __forceinline__ PairCode pair_code(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1) {
+  PairCode p;
+  const uint32_t g7 = lop3<0xB2>(a1, b0, b1);
+  p.p8 = lop3<0x17>(a1, b0, b1);
+  p.p9 = lop3<0xBC>(a0, b0, g7);
+  p.p10 = lop3<0x23>(b0, g7, p.p9);
+  return p;
+}
+__device__ __forceinline__ uint32_t pair_select(const PairCode& p, uint32_t c0, uint32_t c1, uint32_t cell) {
+  const uint32_t g11 = lop3<0xDA>(c0, cell, p.p9);
+  const uint32_t g12 = lop3<0x98>(cell, p.p10, g11);
+  const uint32_t g13 = lop3<0xF1>(c1, g11, g12);
+  return lop3<0x94>(p.p8, g12, g13);
+}
+
 template <int LPP>
 __device__ __forceinline__ Cnt halo(const Cnt& c, int src) {
   if constexpr (LPP == 1) {
@@ -104,24 +128,31 @@ struct Tile {
     for (int k = 0; k < W / 2; k++) p[k] = make_uint4(lo[2 * k], hi[2 * k], lo[2 * k + 1], hi[2 * k + 1]);
   }
 
-  // One generation in place == LifeState::Step() (LifeAPI.hpp:1196-1216), rolling 3-column window.
+  // One generation in place == LifeState::Step() (LifeAPI.hpp:1196-1216).  Words are taken two at a
+  // time: the pair code of (cnt[w], cnt[w+1]) is shared by both words, so a generation costs, per
+  // 32-cell half-word, 2 SHF + 2 LOP3 (column count) + 2 (half a pair code) + 4 (select) = 10
+  // integer-pipe instructions.  Updating in place is safe because every neighbour enters through
+  // column counts taken before the word is overwritten.
   __device__ __forceinline__ void step(int sub) {
+    static_assert(W % 2 == 0, "words are processed in pairs");
     const int up_src = sub + LPP - 1, dn_src = sub + 1;  // taken modulo LPP by shfl width
     Cnt first = count_rows(lo[0], hi[0]);
-    Cnt last = (W == 1) ? first : count_rows(lo[W - 1], hi[W - 1]);
+    Cnt last = count_rows(lo[W - 1], hi[W - 1]);
     Cnt prev = halo<LPP>(last, up_src);
     Cnt after = halo<LPP>(first, dn_src);
-    Cnt cur = first;
+    Cnt c0 = first;
 #pragma unroll
-    for (int w = 0; w < W; w++) {
-      Cnt next;
-      if (w == W - 1) next = after;
-      else if (w + 1 == W - 1) next = last;
-      else next = count_rows(lo[w + 1], hi[w + 1]);
-      uint32_t nlo = rule32(lo[w], prev.b0lo, prev.b1lo, cur.b0lo, cur.b1lo, next.b0lo, next.b1lo);
-      uint32_t nhi = rule32(hi[w], prev.b0hi, prev.b1hi, cur.b0hi, cur.b1hi, next.b0hi, next.b1hi);
-      lo[w] = nlo; hi[w] = nhi;
-      prev = cur; cur = next;
+    for (int w = 0; w < W; w += 2) {
+      const Cnt c1 = (w + 1 == W - 1) ? last : count_rows(lo[w + 1], hi[w + 1]);
+      const Cnt c2 = (w + 2 == W) ? after : (w + 2 == W - 1) ? last : count_rows(lo[w + 2], hi[w + 2]);
+      const PairCode plo = pair_code(c0.b0lo, c0.b1lo, c1.b0lo, c1.b1lo);
+      const PairCode phi = pair_code(c0.b0hi, c0.b1hi, c1.b0hi, c1.b1hi);
+      lo[w] = pair_select(plo, prev.b0lo, prev.b1lo, lo[w]);
+      hi[w] = pair_select(phi, prev.b0hi, prev.b1hi, hi[w]);
+      lo[w + 1] = pair_select(plo, c2.b0lo, c2.b1lo, lo[w + 1]);
+      hi[w + 1] = pair_select(phi, c2.b0hi, c2.b1hi, hi[w + 1]);
+      prev = c1;
+      c0 = c2;
     }
   }
 

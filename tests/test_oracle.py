@@ -300,3 +300,27 @@ def test_port_unknown_step_sop_vs_reference_and_semantics(port, ref):
     r = rng.integers(0, 1 << 63, size=(2, 32, 64), dtype=np.uint64)
     a, b = port.unknown_step_sop_batch(r[0], r[1], 3), ref.unknown_step_batch(r[0], r[1], 3)
     assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
+
+
+def test_pair_shared_rule_luts_exhaustive():
+    """pair_code / pair_select in csrc/life_core.cuh: the code of (a, b) serves both columns of a pair."""
+    import os
+    import re
+    from conftest import ROOT
+    src = open(os.path.join(ROOT, "lifeapi_b200", "csrc", "life_core.cuh")).read()
+    body = src[src.index("PairCode pair_code("):src.index("template <int LPP>\n__device__ __forceinline__ Cnt halo")]
+    assert [int(m, 16) for m in re.findall(r"lop3<(0x\w+)>", body)] == [0xB2, 0x17, 0xBC, 0x23, 0xDA, 0x98, 0xF1, 0x94]
+    for ca in range(4):
+        for cb in range(4):
+            a0, a1, b0, b1 = ca & 1, ca >> 1, cb & 1, cb >> 1
+            g7 = _lop3(0xB2, a1, b0, b1)
+            p8 = _lop3(0x17, a1, b0, b1)
+            p9 = _lop3(0xBC, a0, b0, g7)
+            p10 = _lop3(0x23, b0, g7, p9)
+            for co in range(4):
+                for cell in (0, 1):
+                    g11 = _lop3(0xDA, co & 1, cell, p9)
+                    g12 = _lop3(0x98, cell, p10, g11)
+                    g13 = _lop3(0xF1, co >> 1, g11, g12)
+                    n = ca + cb + co
+                    assert _lop3(0x94, p8, g12, g13) == int(n == 3 or (cell and n == 4))
