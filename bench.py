@@ -31,7 +31,12 @@ sys.path.insert(0, ROOT)
 SEED = 0x4C696665415049
 N_SOUPS = 1 << 20
 GENS = 1024
-INSTR_PER_CELL = 12.0 / 32.0
+INSTR_PER_CELL = 12.0 / 32.0  # algorithmic 2 SHF + 10 LOP3 per 32 cells per generation
+EXECUTED_INSTR_PER_CELL = 10.0 / 32.0  # what step_kernel issues (pair-shared select)
+# dram bytes of one 1 Mi-soup x 1024-generation step_kernel launch from the committed ncu capture
+# (profiles/r01d_step_kernel_lpp4_raw.csv: dram__bytes_read.sum 546.79 MB + dram__bytes_write.sum 488.76 MB;
+# the write side is below 512 MiB because the tail of the output is still in the 126 MB L2 at kernel end)
+STEP_KERNEL_DRAM_BYTES_PER_LAUNCH = 1035547648
 METRIC = "cell_updates_per_sec"
 UNIT = "Gcell/s"
 
@@ -47,6 +52,7 @@ def parse_args():
     ap.add_argument("--lpp", type=int, default=0, help="lanes per pattern override (tuning)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the config 3/4/5 side measurements")
     return ap.parse_args()
 
 
@@ -306,9 +312,15 @@ def main():
     per_gpu_cells_s = n * 4096.0 * gens / (kernel_ms * 1e-3)
     achieved = per_gpu_cells_s * INSTR_PER_CELL
     roofline = {"bound": "int_pipe", "achieved": achieved / 1e12, "peak": p_int / 1e12, "unit": "T lane-instr/s (LOP3+SHF)",
-                "frac": achieved / p_int, "traffic": None,
+                "frac": achieved / p_int,
+                "traffic": STEP_KERNEL_DRAM_BYTES_PER_LAUNCH if (n, gens) == (N_SOUPS, GENS) else None,
+                "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of this launch shape "
+                                  "(profiles/, see DESIGN.md 6); algorithmic = 2 x 512 B x soups",
+                "algorithmic_bytes": 2 * nbytes,
                 "kernel": "step_kernel<LPP>", "kernel_ms": kernel_ms,
                 "algorithmic": "12 int-pipe instr per 32 cells per generation = 0.375 instr/cell-update (SURVEY 8d)",
+                "executed": "10 int-pipe instr per 32 cells per generation (2 SHF + 8 LOP3, pair-shared select)",
+                "pipe_utilisation": per_gpu_cells_s * EXECUTED_INSTR_PER_CELL / p_int,
                 "peak_source": f"LOP3 microbenchmark in this run (lifeb200_measure_int_peak): {p_int / 1e12:.2f} T/s = "
                                f"{info['sm_count']} SMs x 64 lanes x {mhz_eff:.0f} MHz effective",
                 "hbm": {"bound": "hbm", "achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak,
@@ -318,12 +330,16 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_baseline(gens)
+    extras = None
+    if world == 1 and not args.no_extras:
+        from bench_extras import run_extras
+        extras = run_extras(eng, p_int)
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": kernel_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
                 "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e,
-                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "other_configs": extras,
                 "checksum": {"pop_sum": int(pop_sum), "hash_xor": f"{int(hash_xor):016x}"},
                 "lanes_per_pattern": args.lpp or "default", "device": {"sms": info["sm_count"], "cc": list(info["cc"])}}
         print(json.dumps(line), flush=True)

@@ -1,0 +1,193 @@
+"""Side measurements printed in bench.py's `other_configs` (N = 1 only): BASELINE configs 3, 4, 5 and
+the LifeStable Propagate pass.  Not bench lines of their own: the headline stays config 2.  Parity
+of every kernel used here is the job of tests/ (-m gpu); the CPU numbers beside them come from the
+reference compiled into oracle/_ref (bench.py's cpu_baseline leg), on bounded samples."""
+from __future__ import annotations
+
+import time
+
+import numpy as np
+
+SEED = 0x4C696665415049
+
+STILL_LIFES = {  # (x, y) cells
+    "block": [(0, 0), (1, 0), (0, 1), (1, 1)],
+    "tub": [(1, 0), (0, 1), (2, 1), (1, 2)],
+    "boat": [(0, 0), (1, 0), (0, 1), (2, 1), (1, 2)],
+    "ship": [(0, 0), (1, 0), (0, 1), (2, 1), (1, 2), (2, 2)],
+    "beehive": [(1, 0), (2, 0), (0, 1), (3, 1), (1, 2), (2, 2)],
+    "loaf": [(1, 0), (2, 0), (0, 1), (3, 1), (1, 2), (3, 2), (2, 3)],
+    "pond": [(1, 0), (2, 0), (0, 1), (3, 1), (0, 2), (3, 2), (1, 3), (2, 3)],
+    "eater1": [(0, 0), (1, 0), (0, 1), (2, 1), (2, 2), (2, 3), (3, 3)],
+}
+GLIDER = [(1, 0), (2, 1), (0, 2), (1, 2), (2, 2)]
+D4 = [lambda x, y: (x, y), lambda x, y: (3 - x, y), lambda x, y: (x, 3 - y), lambda x, y: (3 - x, 3 - y),
+      lambda x, y: (y, x), lambda x, y: (3 - y, x), lambda x, y: (y, 3 - x), lambda x, y: (3 - y, 3 - x)]
+
+
+def _pattern(cells, ox, oy, tf=None):
+    s = np.zeros(64, dtype=np.uint64)
+    for (x, y) in cells:
+        if tf is not None:
+            x, y = tf(x, y)
+        s[(ox + x) & 63] |= np.uint64(1) << np.uint64((oy + y) & 63)
+    return s
+
+
+def _time(eng, fn, reps=3):
+    fn()
+    eng.sync()
+    eng.timer_start()
+    for _ in range(reps):
+        fn()
+    return eng.timer_stop() / reps
+
+
+def _cpu_ref():
+    try:
+        from oracle.loader import Ref
+        return Ref.load()
+    except Exception:  # noqa: BLE001
+        return None
+
+
+def config3_unknown_step(eng, p_int):
+    """256 Ki partial patterns x 16 three-valued generations (bitslicing/unknown_step.hpp)."""
+    n, gens = 1 << 18, 16
+    d_s, d_u, d_t = eng.malloc(n * 512), eng.malloc(n * 512), eng.malloc(n * 512)
+    try:
+        # state = soup masked to the centred 32x32 box; unknown = AND of three other soups (density 1/8) in the box
+        eng.soup_dev(d_s, 0, n, SEED, 0)
+        host = np.empty((n, 64), dtype=np.uint64)
+        eng.d2h(host, d_s)
+        eng.sync()
+        box = np.zeros(64, dtype=np.uint64)
+        box[16:48] = np.uint64(0x0000FFFFFFFF0000)
+        unk = (np.roll(host, 1, axis=0) & np.roll(host, 2, axis=0) & np.roll(host, 3, axis=0)) & box
+        st = (host & box) & ~unk
+        eng.h2d(d_s, st)
+        eng.h2d(d_u, unk)
+        eng.sync()
+        d_o = eng.malloc(n * 512)
+        ms = _time(eng, lambda: eng.unknown_step_batch_dev(d_s, d_u, d_t, d_o, n, gens))
+        eng.free(d_o)
+        cells = n * 4096.0 * gens
+        out = {"workload": f"config3: {n} partial patterns x {gens} three-valued generations", "ms": ms,
+               "value": cells / (ms * 1e-3) / 1e9, "unit": "Gcell/s",
+               "int_pipe_frac": cells * (40.0 / 32.0) / (ms * 1e-3) / p_int,
+               "algorithmic": "40 int-pipe instr per 32 cells per generation (DESIGN.md 3.3)"}
+        ref = _cpu_ref()
+        if ref is not None:
+            m = 1 << 16
+            t0 = time.perf_counter()
+            ref.unknown_step_batch(st[:m], unk[:m], gens, 0)
+            dt = time.perf_counter() - t0
+            out["cpu_baseline"] = {"value": m * 4096.0 * gens / dt / 1e9, "unit": "Gcell/s", "cores": ref.threads(),
+                                   "kind": "reference", "sample": f"{m} patterns x {gens} gens, {dt:.2f} s"}
+        return out
+    finally:
+        for p in (d_s, d_u, d_t):
+            eng.free(p)
+
+
+def config4_enumeration(eng, p_int):
+    """32 catalysts x 32 glider variants x 4096 offsets = 4 Mi placements, <= 256 gens, fused Contains + hit compaction."""
+    names = list(STILL_LIFES)
+    cats = np.stack([_pattern(STILL_LIFES[names[i % 8]], 28, 28, D4[(i // 8) * 2]) for i in range(32)])
+    g0 = np.stack([_pattern(GLIDER, 8, 8, tf) for tf in D4])
+    phases = [g0]
+    for _ in range(3):
+        phases.append(eng.step_batch_host(phases[-1], 1))  # glider phases from the product path itself
+    gliders = np.ascontiguousarray(np.stack(phases, axis=1).reshape(32, 64))
+    total = 32 * 32 * 4096
+    gens, interval = 256, 8
+    t0 = time.perf_counter()
+    hits, skipped = eng.enumerate_collisions(cats, gliders, 0, total, gens, interval, 1 << 20)
+    dt = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    hits, skipped = eng.enumerate_collisions(cats, gliders, 0, total, gens, interval, 1 << 20)
+    dt = min(dt, time.perf_counter() - t0)
+    out = {"workload": f"config4: {total} placements (32 catalysts x 32 glider variants x 4096 offsets), <= {gens} gens, "
+                       f"stable_interval {interval}", "s": dt, "placements_per_s": total / dt, "hits": int(len(hits)),
+           "skipped_overlapping": int(skipped), "timing": "wall clock around the host-facing C-ABI call (tables up, hits down, sorted)"}
+    ref = _cpu_ref()
+    if ref is not None:
+        m = 1 << 14
+        t0 = time.perf_counter()
+        ids, ff, rec, sk = ref.enumerate(cats, gliders, 0, m, gens, interval, m)
+        dt_cpu = time.perf_counter() - t0
+        sub = hits[hits["id"] < m]
+        out["cpu_baseline"] = {"placements_per_s": m / dt_cpu, "cores": 1, "kind": "reference",
+                               "sample": f"first {m} placement ids, {dt_cpu:.2f} s, 1 thread",
+                               "hits_equal_on_sample": bool(len(sub) == len(ids) and (sub["id"] == ids).all()
+                                                            and (sub["g_first_false"] == ff).all() and (sub["g_recovered"] == rec).all())}
+    return out
+
+
+def config5_survey(eng, p_int):
+    """Soups generated on device, 4096 gens, activity test + hit compaction (1/16 of the 16 Mi-soup config per call)."""
+    n, gens = 1 << 20, 4096
+    t0 = time.perf_counter()
+    hits, pop_sum, hash_xor = eng.soup_survey(0, n, SEED, 0, gens, n)
+    dt = time.perf_counter() - t0
+    cells = n * 4096.0 * gens
+    return {"workload": f"config5 (1/16 scale): {n} on-device soups x {gens} gens, active iff state(G) != state(G-2)", "s": dt,
+            "value": cells / dt / 1e9, "unit": "Gcell/s", "active": int(len(hits)), "pop_sum": int(pop_sum),
+            "hash_xor": f"{int(hash_xor):016x}", "int_pipe_frac_executed": cells * (10.0 / 32.0) / dt / p_int,
+            "timing": "wall clock around the host-facing call, hits downloaded and sorted"}
+
+
+def stable_propagate(eng, p_int):
+    """LifeStable::Propagate on 64 Ki records (320 MiB resident)."""
+    import sys
+    import os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests"))
+    from stable_inputs import stable_records
+    base = stable_records(512, 5)
+    n = 1 << 16
+    recs = np.ascontiguousarray(np.tile(base, (n // 512, 1, 1)))
+    d, d_f, d_w = eng.malloc(recs.nbytes), eng.malloc(n), eng.malloc(recs.nbytes)
+    try:
+        eng.h2d(d, recs)
+        eng.sync()
+
+        def once():
+            eng._check(eng.lib.lifeb200_memset(eng._h, d_f, 0, n))
+            eng._check(_d2d(eng, d_w, d, recs.nbytes))
+            eng.stable_pass_dev(d_w, n, 5, d_f)
+        ms = _time(eng, once)
+        ms_copy = _time(eng, lambda: eng._check(_d2d(eng, d_w, d, recs.nbytes)))
+        flags = np.zeros(n, dtype=np.uint8)
+        eng.d2h(flags, d_f)
+        eng.sync()
+        out = {"workload": f"LifeStable::Propagate to the fixed point on {n} records (5120 B each)", "ms": ms - ms_copy,
+               "records_per_s": n / ((ms - ms_copy) * 1e-3), "consistent": int((flags & 1).sum()),
+               "hbm_gbs": 2 * recs.nbytes / ((ms - ms_copy) * 1e-3) / 1e9}
+        ref = _cpu_ref()
+        if ref is not None:
+            m = 1 << 15
+            t0 = time.perf_counter()
+            ref.stable_pass_batch(recs[:m], 5, 0)
+            dt = time.perf_counter() - t0
+            out["cpu_baseline"] = {"records_per_s": m / dt, "cores": ref.threads(), "kind": "reference",
+                                   "sample": f"{m} records, {dt:.2f} s (includes one copy of the sample)"}
+        return out
+    finally:
+        for p in (d, d_f, d_w):
+            eng.free(p)
+
+
+def _d2d(eng, dst, src, nbytes):
+    # device-to-device copy through the step entry point's gens == 0 path (a plain cudaMemcpyAsync D2D)
+    return eng.lib.lifeb200_step_batch_dev(eng._h, src, dst, nbytes // 512, 0)
+
+
+def run_extras(eng, p_int):
+    out = {}
+    for name, fn in (("config3", config3_unknown_step), ("config4", config4_enumeration), ("config5", config5_survey),
+                     ("stable_propagate", stable_propagate)):
+        try:
+            out[name] = fn(eng, p_int)
+        except Exception as e:  # noqa: BLE001  (a side measurement must not kill the headline)
+            out[name] = {"error": repr(e)}
+    return out

@@ -9,6 +9,7 @@
 //   LifeTarget  { wanted, unwanted }                                     LifeTarget.hpp:5-18
 //   NeighbourCount { bit3, bit2, bit1, bit0 }                            NeighbourCount.hpp:7-102
 //   LifeHistory { state, history, marked, original }                     LifeHistory.hpp:8-12
+//   LifeStable  { state, unknown, live2, live3, dead0..dead6 } + full-grid passes  LifeStable.hpp:39-53,366-729
 //
 // Every stepping member is a batch of ONE through the same sm_100a kernels the batched API uses;
 // there is NO CPU implementation of Step in this header and no fallback: if the library cannot
@@ -203,9 +204,87 @@ static_assert(sizeof(NeighbourCount) == 2048, "NeighbourCount layout (NeighbourC
 // LifeHistory.hpp:8-12: passive 4-plane container (no Step in the reference).
 struct LifeHistory {
   LifeState state, history, marked, original;
-  // build-defined accumulate step: state.Step(n) then history |= state
-  void StepAccumulate(unsigned n = 1) { for (unsigned i = 0; i < n; i++) { state.Step(); history |= state; } }
+  // build-defined accumulate step: n times { state.Step(); history |= state; } in one launch
+  void StepAccumulate(unsigned n = 1) {
+    lifeb200_ctx* ctx = lifeb200::DefaultContext();
+    void* d = nullptr;
+    lifeb200::Check(lifeb200_malloc(ctx, &d, sizeof *this), "malloc");
+    lifeb200::Check(lifeb200_memcpy_h2d(ctx, d, this, sizeof *this), "h2d");
+    lifeb200::Check(lifeb200_history_step_batch_dev(ctx, static_cast<uint64_t*>(d), 1, n), "StepAccumulate");
+    lifeb200::Check(lifeb200_memcpy_d2h(ctx, this, d, sizeof *this), "d2h");
+    lifeb200::Check(lifeb200_sync(ctx), "sync");
+    lifeb200::Check(lifeb200_free(ctx, d), "free");
+  }
 };
+static_assert(sizeof(LifeHistory) == 2048, "LifeHistory layout (LifeHistory.hpp:8-12)");
+
+// LifeStable.hpp:36-131: the 10 planes in the reference's declaration order; option planes are
+// stored inverted (1 = ruled out, LifeStable.hpp:44-46).  The full-grid propagation passes run on
+// the GPU and leave *this exactly as the reference members do; the strip variants and the
+// CompleteStable search are not part of this header.
+struct LifeStable {
+  LifeState state, unknown, live2, live3, dead0, dead1, dead2, dead4, dead5, dead6;
+
+  struct PropagateResult {
+    bool consistent;
+    bool changed;
+  };
+
+  bool operator==(const LifeStable& o) const { return std::memcmp(this, &o, sizeof *this) == 0; }
+
+  void SetOn(const LifeState& which) {  // LifeStable.hpp:320-328
+    state |= which; unknown &= ~which;
+    dead0 |= which; dead1 |= which; dead2 |= which; dead4 |= which; dead5 |= which; dead6 |= which;
+  }
+  void SetOff(const LifeState& which) {  // LifeStable.hpp:329-335
+    state &= ~which; unknown &= ~which; live2 |= which; live3 |= which;
+  }
+
+  PropagateResult PropagateSimpleStep() { return Run(LIFEB200_STABLE_PROPAGATE_SIMPLE_STEP); }  // :414-503
+  PropagateResult PropagateSimple() { return Run(LIFEB200_STABLE_PROPAGATE_SIMPLE); }           // :505-524
+  PropagateResult SynchroniseStateKnown() { return Run(LIFEB200_STABLE_SYNCHRONISE); }          // :526-556
+  PropagateResult UpdateOptions() { return Run(LIFEB200_STABLE_UPDATE_OPTIONS); }               // :558-615
+  PropagateResult SignalNeighbours() { return Run(LIFEB200_STABLE_SIGNAL_NEIGHBOURS); }         // :617-675
+  PropagateResult StabiliseOptions() { return Run(LIFEB200_STABLE_STABILISE_OPTIONS); }         // :677-693
+  PropagateResult PropagateStep() { return Run(LIFEB200_STABLE_PROPAGATE_STEP); }               // :695-716
+  PropagateResult Propagate() { return Run(LIFEB200_STABLE_PROPAGATE); }                        // :718-729
+
+  LifeState Vulnerable() const {  // :366-412
+    lifeb200_ctx* ctx = lifeb200::DefaultContext();
+    void *d = nullptr, *o = nullptr;
+    LifeState out;
+    lifeb200::Check(lifeb200_malloc(ctx, &d, sizeof *this), "malloc");
+    lifeb200::Check(lifeb200_malloc(ctx, &o, sizeof out), "malloc");
+    lifeb200::Check(lifeb200_memcpy_h2d(ctx, d, this, sizeof *this), "h2d");
+    lifeb200::Check(lifeb200_stable_vulnerable_dev(ctx, static_cast<const uint64_t*>(d), static_cast<uint64_t*>(o), 1), "Vulnerable");
+    lifeb200::Check(lifeb200_memcpy_d2h(ctx, out.state, o, sizeof out), "d2h");
+    lifeb200::Check(lifeb200_sync(ctx), "sync");
+    lifeb200_free(ctx, d);
+    lifeb200_free(ctx, o);
+    return out;
+  }
+
+  // batched form: one pass (LIFEB200_STABLE_*) over an array of records, results[i] per record
+  static void PassBatch(LifeStable* recs, size_t n, int pass, PropagateResult* results, lifeb200_ctx* ctx = nullptr) {
+    std::vector<uint8_t> flags(n);
+    lifeb200::Check(lifeb200_stable_pass_host(ctx ? ctx : lifeb200::DefaultContext(), reinterpret_cast<uint64_t*>(recs), n,
+                                              pass, flags.data()), "LifeStable::PassBatch");
+    if (results)
+      for (size_t i = 0; i < n; i++)
+        results[i] = {(flags[i] & LIFEB200_STABLE_CONSISTENT) != 0, (flags[i] & LIFEB200_STABLE_CHANGED) != 0};
+  }
+  static void PropagateBatch(LifeStable* recs, size_t n, PropagateResult* results, lifeb200_ctx* ctx = nullptr) {
+    PassBatch(recs, n, LIFEB200_STABLE_PROPAGATE, results, ctx);
+  }
+
+ private:
+  PropagateResult Run(int pass) {
+    PropagateResult r;
+    PassBatch(this, 1, pass, &r);
+    return r;
+  }
+};
+static_assert(sizeof(LifeStable) == LIFEB200_STABLE_BYTES, "LifeStable layout (LifeStable.hpp:39-53)");
 
 // ---------------------------------------------------------------------------------------------
 // Batched API: a std::vector<LifeState> is already the flat AoS batch.

@@ -18,6 +18,8 @@ void lo_step_alt(uint64_t* s);
 void lo_step_n(uint64_t* s, unsigned gens);
 void lo_neighbour_count(const uint64_t* s, uint64_t* planes);
 int lo_contains_target(const uint64_t* s, const uint64_t* target);
+unsigned lo_stable_pass(uint64_t* planes, int pass);
+void lo_stable_vulnerable(const uint64_t* planes, uint64_t* out);
 }
 
 static int failures = 0;
@@ -108,7 +110,45 @@ static void NeighbourCount_And_Target() {
   }
 }
 
+// LifeStable members (LifeStable.hpp:414-729) and the LifeHistory accumulate step through the header.
+static void Stable_And_History() {
+  LifeStable st;
+  // a block and a beehive with a few cells unknown (state &= ~unknown), all options open
+  st.state = LifeState::Parse("2o$2o!", 10, 10) | LifeState::Parse("b2o$o2bo$b2o!", 30, 20);
+  st.unknown = LifeState::Parse("3o$3o!", 9, 9) | LifeState::Parse("2o!", 31, 20);
+  st.state &= ~st.unknown;
+  for (int pass : {LIFEB200_STABLE_SYNCHRONISE, LIFEB200_STABLE_UPDATE_OPTIONS, LIFEB200_STABLE_SIGNAL_NEIGHBOURS,
+                   LIFEB200_STABLE_PROPAGATE_SIMPLE_STEP, LIFEB200_STABLE_PROPAGATE}) {
+    LifeStable want = st;
+    unsigned wf = lo_stable_pass(reinterpret_cast<uint64_t*>(&want), pass);
+    LifeStable got = st;
+    LifeStable::PropagateResult r{};
+    LifeStable::PassBatch(&got, 1, pass, &r);
+    EXPECT_EQ(got, want);
+    EXPECT_EQ(r.consistent, (wf & 1u) != 0);
+    EXPECT_EQ(r.changed, (wf & 2u) != 0);
+  }
+  LifeStable done = st;
+  auto res = done.Propagate();
+  EXPECT_TRUE(res.consistent);
+  auto again = done.Propagate();
+  EXPECT_TRUE(again.consistent && !again.changed);
+  LifeState v = done.Vulnerable(), vw;
+  lo_stable_vulnerable(reinterpret_cast<const uint64_t*>(&done), vw.state);
+  EXPECT_EQ(v, vw);
+
+  LifeHistory h;
+  h.state = LifeState::Parse("b2o$2o$bo!", 20, 20);
+  h.history = h.state;
+  LifeState cur = h.state, acc = h.state;
+  for (int g = 0; g < 40; g++) { lo_step(cur.state); acc |= cur; }
+  h.StepAccumulate(40);
+  EXPECT_EQ(h.state, cur);
+  EXPECT_EQ(h.history, acc);
+}
+
 int main() {
+  Stable_And_History();
   StepAltTest_Random();
   StepN_RPentomino();
   Batch_MatchesSingles();
