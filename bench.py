@@ -261,9 +261,29 @@ def main():
 
     # ---- counters / checksum gathered over NCCL (the path's only collective) --------
     pop_sum, hash_xor = eng.fold_dev(d_out, n, first_id)
+    survey_gather = None
     if distributed:
         _, sums, xors = gather_hits(np.zeros(0, dtype=HIT_DTYPE), [pop_sum, hash_xor], device=dev)
         pop_sum, hash_xor = sums[0], xors[1]
+        # config 5 shape: each rank surveys its shard of one global id range on device, then the hit
+        # lists and counters are gathered over NCCL (the path's only collective)
+        from lifeapi_b200 import shard_range
+        total5, gens5 = world << 18, 1024
+        lo, hi = shard_range(total5, rank, world)
+        barrier()
+        t0 = time.perf_counter()
+        hits5, ps5, hx5 = eng.soup_survey(lo, hi - lo, SEED, 0, gens5, hi - lo)
+        t_local = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        merged, sums5, xors5 = gather_hits(hits5, [ps5, hx5], device=dev)
+        torch.cuda.synchronize()
+        t_gather = max_over_ranks(time.perf_counter() - t0)
+        t_local = max_over_ranks(t_local)
+        survey_gather = {"workload": f"config5 shape: {total5} on-device soups x {gens5} gens sharded by id over {world} ranks",
+                         "active_hits_total": int(len(merged)), "hits_sorted_unique": bool((np.diff(merged["id"].astype(np.int64)) > 0).all()),
+                         "pop_sum": int(sums5[0]), "hash_xor": f"{int(xors5[1]):016x}", "survey_s": t_local,
+                         "gather_s": t_gather, "gather_bytes": int(len(merged)) * 16,
+                         "value": total5 * 4096.0 * gens5 / (t_local + t_gather) / 1e9, "unit": UNIT}
 
     # ---- HBM-bound companion: one generation per launch (load/store phases dominate) -----------
     for _ in range(3):
@@ -339,7 +359,7 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": kernel_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
                 "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e,
-                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "other_configs": extras,
+                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "other_configs": extras, "survey_gather": survey_gather,
                 "checksum": {"pop_sum": int(pop_sum), "hash_xor": f"{int(hash_xor):016x}"},
                 "lanes_per_pattern": args.lpp or "default", "device": {"sms": info["sm_count"], "cc": list(info["cc"])}}
         print(json.dumps(line), flush=True)

@@ -149,6 +149,34 @@ struct alignas(64) LifeState {
     std::memcpy(bit1.state, planes + 2 * N, 512); std::memcpy(bit0.state, planes + 3 * N, 512);
   }
 
+  // GetHash (LifeAPI.hpp:373): XXH3_64bits of the 512-byte state, computed on the GPU
+  uint64_t GetHash() const {
+    uint64_t h = 0;
+    lifeb200::Check(lifeb200_hash_batch_host(lifeb200::DefaultContext(), state, &h, 1), "GetHash");
+    return h;
+  }
+
+  // InteractionCounts / InteractionCountsAndNext (LifeAPI.hpp:956-1040)
+  void InteractionCountsAndNext(LifeState& out1, LifeState& out2, LifeState& outMore, LifeState& next) const {
+    lifeb200_ctx* ctx = lifeb200::DefaultContext();
+    void *d = nullptr, *o = nullptr;
+    alignas(64) uint64_t planes[4 * N];
+    lifeb200::Check(lifeb200_malloc(ctx, &d, sizeof state), "malloc");
+    lifeb200::Check(lifeb200_malloc(ctx, &o, sizeof planes), "malloc");
+    lifeb200::Check(lifeb200_memcpy_h2d(ctx, d, state, sizeof state), "h2d");
+    lifeb200::Check(lifeb200_interaction_counts_dev(ctx, static_cast<const uint64_t*>(d), static_cast<uint64_t*>(o), 1), "InteractionCounts");
+    lifeb200::Check(lifeb200_memcpy_d2h(ctx, planes, o, sizeof planes), "d2h");
+    lifeb200::Check(lifeb200_sync(ctx), "sync");
+    lifeb200_free(ctx, d);
+    lifeb200_free(ctx, o);
+    std::memcpy(out1.state, planes, 512); std::memcpy(out2.state, planes + N, 512);
+    std::memcpy(outMore.state, planes + 2 * N, 512); std::memcpy(next.state, planes + 3 * N, 512);
+  }
+  void InteractionCounts(LifeState& out1, LifeState& out2, LifeState& outMore) const {
+    LifeState next;
+    InteractionCountsAndNext(out1, out2, outMore, next);
+  }
+
   bool Contains(const LifeTarget& target) const;  // LifeTarget.hpp:44-51 (defined below)
   bool Contains(const LifeState& pat) const { return (*this & pat) == pat; }                 // :388-397
   bool AreDisjoint(const LifeState& pat) const { return (*this & pat).IsEmpty(); }          // :377-386
@@ -217,6 +245,38 @@ struct LifeHistory {
   }
 };
 static_assert(sizeof(LifeHistory) == 2048, "LifeHistory layout (LifeHistory.hpp:8-12)");
+
+// LifeWeld.hpp:18-63,169-191: state + frozen neighbour counts; Step adds the frozen count to the true
+// 3x3 count before the rule.  Runs on the GPU (lifeb200_weld_step_batch_dev).
+struct LifeWeld {
+  LifeState state, frozen2, frozen1, frozen0;
+  LifeWeld() = default;
+  LifeWeld(const LifeState& s) : state{s} {}
+  LifeWeld(const LifeState& s, const LifeState& f2, const LifeState& f1, const LifeState& f0)
+      : state{s}, frozen2{f2}, frozen1{f1}, frozen0{f0} {}
+  bool operator==(const LifeWeld& o) const { return std::memcmp(this, &o, sizeof *this) == 0; }
+  LifeState AllFrozen() const { return frozen2 | frozen1 | frozen0; }
+  bool Contains(const LifeTarget& target) const { return state.Contains(target); }
+  uint64_t GetHash() const {  // LifeWeld.hpp:61-63
+    return 3 * frozen2.GetHash() + (3 * frozen1.GetHash() + (3 * frozen0.GetHash() + state.GetHash()));
+  }
+  void Step(unsigned numIters = 1) {  // LifeWeld.hpp:169-186
+    lifeb200_ctx* ctx = lifeb200::DefaultContext();
+    void* d = nullptr;
+    lifeb200::Check(lifeb200_malloc(ctx, &d, sizeof *this), "malloc");
+    lifeb200::Check(lifeb200_memcpy_h2d(ctx, d, this, sizeof *this), "h2d");
+    lifeb200::Check(lifeb200_weld_step_batch_dev(ctx, static_cast<uint64_t*>(d), 1, numIters), "LifeWeld::Step");
+    lifeb200::Check(lifeb200_memcpy_d2h(ctx, this, d, sizeof *this), "d2h");
+    lifeb200::Check(lifeb200_sync(ctx), "sync");
+    lifeb200::Check(lifeb200_free(ctx, d), "free");
+  }
+  LifeTarget ToTarget() const;  // LifeWeld.hpp:188-191 (defined after LifeTarget)
+};
+static_assert(sizeof(LifeWeld) == 2048, "LifeWeld layout (LifeWeld.hpp:18-22)");
+inline LifeTarget LifeWeld::ToTarget() const {
+  const LifeState nonFrozen = state & ~frozen2 & ~frozen1 & ~frozen0;
+  return LifeTarget(state, nonFrozen.ZOI() & ~state);
+}
 
 // LifeStable.hpp:36-131: the 10 planes in the reference's declaration order; option planes are
 // stored inverted (1 = ruled out, LifeStable.hpp:44-46).  The full-grid propagation passes run on

@@ -184,6 +184,19 @@ int lifeb200_unknown_step_refined_dev(lifeb200_ctx* ctx, const uint64_t* records
                                       const uint64_t* current_unknown, size_t n, int variant, uint64_t* next_on,
                                       uint64_t* next_unknown, uint64_t* next_unknown_stable);
 
+/* ---- 8f "next" rows: the callers and formats either side of the stepping path ------------
+ * LifeWeld::Step (LifeWeld.hpp:169-186): record = state, frozen2, frozen1, frozen0 = 2048 B
+ * (LifeWeld.hpp:18-22); per generation the 3x3 count (bit3 dropped, as the reference does) plus
+ * the frozen count feeds the B3/S23 rule.  In place, `gens` generations per launch. */
+int lifeb200_weld_step_batch_dev(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens);
+/* LifeState::InteractionCountsAndNext (LifeAPI.hpp:997-1040; the first three planes are
+ * InteractionCounts, :956-995): planes[p] = out1, out2, outMore, next (4 x 512 B). */
+int lifeb200_interaction_counts_dev(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n);
+/* LifeState::GetHash (LifeAPI.hpp:373) = XXH3_64bits(state, 512) with the default secret
+ * (xxHash v0.8.3, the reference's vendored submodule): hashes[p] for p < n. */
+int lifeb200_hash_batch_dev(lifeb200_ctx* ctx, const uint64_t* patterns, uint64_t* hashes, size_t n);
+int lifeb200_hash_batch_host(lifeb200_ctx* ctx, const uint64_t* patterns, uint64_t* hashes, size_t n);
+
 /* ---- roofline denominator: measured LOP3 lane-instructions per second ------------------- */
 int lifeb200_measure_int_peak(lifeb200_ctx* ctx, double* lop3_lane_instr_per_s, double* sm_mhz_effective);
 

@@ -85,6 +85,10 @@ SIGNATURES = {
     "lifeb200_stable_pass_host": (C.c_int, [_vp, _vp, C.c_size_t, C.c_int, _vp]),
     "lifeb200_stable_vulnerable_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "lifeb200_unknown_step_refined_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp, _vp]),
+    "lifeb200_weld_step_batch_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_uint]),
+    "lifeb200_interaction_counts_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_hash_batch_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_hash_batch_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "lifeb200_measure_int_peak": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 }
 
@@ -387,3 +391,50 @@ class Engine:
             for b in bufs:
                 self.free(b)
         return tuple(outs)
+
+    # -- 8f next rows: LifeWeld::Step, InteractionCountsAndNext, GetHash -------------------------------
+    def _roundtrip(self, src: np.ndarray, out_shape, out_dtype, call) -> np.ndarray:
+        src = np.ascontiguousarray(src)
+        out = np.empty(out_shape, dtype=out_dtype)
+        d_in, d_out = self.malloc(max(src.nbytes, 16)), self.malloc(max(out.nbytes, 16))
+        try:
+            self.h2d(d_in, src)
+            call(d_in, d_out)
+            if out.nbytes:
+                self.d2h(out, d_out)
+            self.sync()
+        finally:
+            self.free(d_in)
+            self.free(d_out)
+        return out
+
+    def weld_step_batch(self, records: np.ndarray, gens: int) -> np.ndarray:
+        """(n, 4, 64) LifeWeld records (state, frozen2, frozen1, frozen0) stepped `gens` generations."""
+        records = np.ascontiguousarray(records, dtype=np.uint64)
+        n = records.size // (4 * WORDS)
+        out = np.empty_like(records)
+        d = self.malloc(max(records.nbytes, 16))
+        try:
+            self.h2d(d, records)
+            self._check(self.lib.lifeb200_weld_step_batch_dev(self._h, d, n, gens))
+            self.d2h(out, d)
+            self.sync()
+        finally:
+            self.free(d)
+        return out
+
+    def interaction_counts(self, patterns: np.ndarray) -> np.ndarray:
+        patterns = np.ascontiguousarray(patterns, dtype=np.uint64)
+        n = patterns.size // WORDS
+        return self._roundtrip(patterns, (n, 4, WORDS), np.uint64,
+                               lambda di, do: self._check(self.lib.lifeb200_interaction_counts_dev(self._h, di, do, n)))
+
+    def hash_batch_dev(self, d_patterns, d_hashes, n: int) -> None:
+        self._check(self.lib.lifeb200_hash_batch_dev(self._h, _ptr(d_patterns), _ptr(d_hashes), n))
+
+    def hash_batch_host(self, patterns: np.ndarray) -> np.ndarray:
+        patterns = np.ascontiguousarray(patterns, dtype=np.uint64)
+        n = patterns.size // WORDS
+        out = np.empty(n, dtype=np.uint64)
+        self._check(self.lib.lifeb200_hash_batch_host(self._h, _ptr(patterns), _ptr(out), n))
+        return out

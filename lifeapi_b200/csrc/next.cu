@@ -1,0 +1,202 @@
+// next.cu -- the callers and data formats either side of the stepping path:
+//   LifeWeld::Step (LifeWeld.hpp:169-186), InteractionCounts / InteractionCountsAndNext
+//   (LifeAPI.hpp:956-1040) and LifeState::GetHash = XXH3_64bits of the 512-byte state
+//   (LifeAPI.hpp:373), each batched over whole patterns held in registers.
+#include <algorithm>
+
+#include "ctx.h"
+#include "life_core.cuh"
+#include "xxh3_keys.h"
+
+namespace lifeb200 {
+
+constexpr int kBlockN = 256;
+static inline unsigned grid_n(size_t n, int lpp) { return (unsigned)((n * (size_t)lpp + kBlockN - 1) / kBlockN); }
+
+// ---- LifeWeld::Step: 3x3 count (bit3 dropped, as the reference does) + frozen count, then the rule ----
+template <int LPP>
+__global__ void __launch_bounds__(kBlockN) weld_step_kernel(uint64_t* __restrict__ records, size_t n, unsigned gens) {
+  constexpr int W = Tile<LPP>::W;
+  const size_t p = ((size_t)blockIdx.x * kBlockN + threadIdx.x) / LPP;
+  const int sub = threadIdx.x & (LPP - 1);
+  const bool valid = p < n;
+  Tile<LPP> s, f2, f1, f0;
+  if (valid) {
+    uint64_t* r = records + p * 4 * kN;  // state, frozen2, frozen1, frozen0 (LifeWeld.hpp:18-22)
+    s.load(r, sub); f2.load(r + kN, sub); f1.load(r + 2 * kN, sub); f0.load(r + 3 * kN, sub);
+  } else {
+#pragma unroll
+    for (int w = 0; w < W; w++) s.lo[w] = s.hi[w] = f2.lo[w] = f2.hi[w] = f1.lo[w] = f1.hi[w] = f0.lo[w] = f0.hi[w] = 0;
+  }
+#pragma unroll 1
+  for (unsigned g = 0; g < gens; g++) {
+    Tile<LPP> b3, b2, b1, b0;
+    s.neighbour_count(sub, b3, b2, b1, b0);
+#pragma unroll
+    for (int k = 0; k < 2 * W; k++) {
+      const uint32_t sum0 = reg(b0, k) ^ reg(f0, k), c0 = reg(b0, k) & reg(f0, k);        // HalfAdd
+      const uint32_t sum1 = lop3<kXor3>(reg(b1, k), reg(f1, k), c0), c1 = lop3<kMaj>(reg(b1, k), reg(f1, k), c0);
+      const uint32_t sum2 = lop3<kXor3>(reg(b2, k), reg(f2, k), c1);                     // carry2 unused
+      const uint32_t t = (sum0 ^ sum2) & (sum1 ^ sum2);
+      reg(s, k) = t & (reg(s, k) | sum0);
+    }
+  }
+  if (valid) s.store(records + p * 4 * kN, sub);
+}
+
+// ---- InteractionCounts[AndNext]: out1, out2, outMore (+ next), the reference's formulas verbatim ----
+template <int LPP>
+__global__ void __launch_bounds__(kBlockN) interaction_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
+                                                              size_t n) {
+  constexpr int W = Tile<LPP>::W;
+  const size_t p = ((size_t)blockIdx.x * kBlockN + threadIdx.x) / LPP;
+  const int sub = threadIdx.x & (LPP - 1);
+  const bool valid = p < n;  // invalid groups still take part in the full-warp shuffles
+  Tile<LPP> s, o1, o2, om, nx;
+  if (valid) s.load(in + p * kN, sub);
+  else {
+#pragma unroll
+    for (int w = 0; w < W; w++) s.lo[w] = s.hi[w] = 0;
+  }
+  const int up_src = sub + LPP - 1, dn_src = sub + 1;
+  Cnt first = count_rows(s.lo[0], s.hi[0]);
+  Cnt last = count_rows(s.lo[W - 1], s.hi[W - 1]);
+  Cnt prev = halo<LPP>(last, up_src);
+  Cnt after = halo<LPP>(first, dn_src);
+  Cnt cur = first;
+#pragma unroll
+  for (int w = 0; w < W; w++) {
+    Cnt next = (w == W - 1) ? after : (w + 1 == W - 1) ? last : count_rows(s.lo[w + 1], s.hi[w + 1]);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const uint32_t a = h ? s.hi[w] : s.lo[w];
+      const uint32_t u0 = h ? prev.b0hi : prev.b0lo, u1 = h ? prev.b1hi : prev.b1lo;
+      const uint32_t c0 = h ? cur.b0hi : cur.b0lo, c1 = h ? cur.b1hi : cur.b1lo;
+      const uint32_t l0 = h ? next.b0hi : next.b0lo, l1 = h ? next.b1hi : next.b1lo;
+      const uint32_t fs = lop3<kXor3>(u0, c0, l0), fc = lop3<kMaj>(u0, c0, l0);
+      const uint32_t cs = lop3<kXor3>(u1, c1, l1);
+      uint32_t cc = lop3<kMaj>(u1, c1, l1);
+      const uint32_t r1 = ~a & ~cc & fs & ~cs & ~fc;
+      const uint32_t r2 = ~a & ~cc & ~fs & (cs ^ fc);
+      const uint32_t rm = ~a & ~r2 & (fc | cs | cc);
+      cc = cc ^ (cs & fc);
+      const uint32_t nn = (fs ^ cc) & (fc ^ cs ^ cc) & (a | fs);
+      if (h) { o1.hi[w] = r1; o2.hi[w] = r2; om.hi[w] = rm; nx.hi[w] = nn; }
+      else { o1.lo[w] = r1; o2.lo[w] = r2; om.lo[w] = rm; nx.lo[w] = nn; }
+    }
+    prev = cur; cur = next;
+  }
+  if (!valid) return;
+  uint64_t* o = out + p * 4 * kN;
+  o1.store(o, sub); o2.store(o + kN, sub); om.store(o + 2 * kN, sub); nx.store(o + 3 * kN, sub);
+}
+
+// ---- XXH3_64bits(state, 512): 8 stripes of 64 bytes; 8 lanes per pattern, one stripe per lane ----
+__constant__ uint64_t c_stripe_keys[8][8] = {LIFEB200_XXH3_STRIPE_KEYS};
+__constant__ uint64_t c_merge_keys[8] = {LIFEB200_XXH3_MERGE_KEYS};
+
+__device__ __forceinline__ uint64_t fold128(uint64_t a, uint64_t b) { return (a * b) ^ __umul64hi(a, b); }
+
+__global__ void __launch_bounds__(kBlockN) hash_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ hashes,
+                                                       size_t n) {
+  constexpr int LPP = 8;
+  const size_t p = ((size_t)blockIdx.x * kBlockN + threadIdx.x) / LPP;
+  const int sub = threadIdx.x & (LPP - 1);  // = stripe index
+  const bool valid = p < n;
+  Tile<LPP> t;
+  if (valid) t.load(in + p * kN, sub);
+  else {
+#pragma unroll
+    for (int w = 0; w < 8; w++) t.lo[w] = t.hi[w] = 0;
+  }
+  // accumulate_512 of this lane's stripe; sums commute, so stripes are added across lanes afterwards
+  uint64_t acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) acc[i] = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const uint64_t d = ((uint64_t)t.hi[i] << 32) | t.lo[i];
+    const uint64_t k = d ^ c_stripe_keys[sub][i];
+    acc[i ^ 1] += d;
+    acc[i] += (k & 0xffffffffULL) * (k >> 32);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o, 8);
+  }
+  if (valid && sub == 0) {
+    const uint64_t init[8] = {xxh3::kPrime32_3, xxh3::kPrime64_1, xxh3::kPrime64_2, xxh3::kPrime64_3,
+                              xxh3::kPrime64_4, xxh3::kPrime32_2, xxh3::kPrime64_5, xxh3::kPrime32_1};
+    uint64_t r = 512ULL * xxh3::kPrime64_1;
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+      r += fold128((acc[2 * k] + init[2 * k]) ^ c_merge_keys[2 * k], (acc[2 * k + 1] + init[2 * k + 1]) ^ c_merge_keys[2 * k + 1]);
+    r ^= r >> 37;
+    r *= xxh3::kPrimeMx1;
+    r ^= r >> 32;
+    hashes[p] = r;
+  }
+}
+
+}  // namespace lifeb200
+
+using namespace lifeb200;
+
+extern "C" {
+
+int lifeb200_weld_step_batch_dev(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0 || gens == 0) return LIFEB200_OK;
+  if (!records || !aligned16(records)) return set_error(LIFEB200_E_ARG, "bad record pointer");
+  int lpp = std::max(8, effective_lpp(ctx));  // 8 tiles live: keep W <= 8
+  LIFEB200_DISPATCH_LPP(lpp, (weld_step_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, ctx->stream>>>(records, n, gens)));
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+int lifeb200_interaction_counts_dev(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (!in || !planes || !aligned16(in) || !aligned16(planes)) return set_error(LIFEB200_E_ARG, "null or misaligned pointer");
+  int lpp = std::max(8, effective_lpp(ctx));
+  LIFEB200_DISPATCH_LPP(lpp, (interaction_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, ctx->stream>>>(in, planes, n)));
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+int lifeb200_hash_batch_dev(lifeb200_ctx* ctx, const uint64_t* patterns, uint64_t* hashes, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (!patterns || !hashes || !aligned16(patterns)) return set_error(LIFEB200_E_ARG, "null or misaligned pointer");
+  hash_kernel<<<grid_n(n, 8), kBlockN, 0, ctx->stream>>>(patterns, hashes, n);
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+int lifeb200_hash_batch_host(lifeb200_ctx* ctx, const uint64_t* patterns, uint64_t* hashes, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (!patterns || !hashes) return set_error(LIFEB200_E_ARG, "null pointer");
+  const size_t chunk = std::min<size_t>(n, (size_t)1 << 16);
+  const size_t nchunks = (n + chunk - 1) / chunk;
+  const int used = (int)std::min<size_t>(kSlots, nchunks);
+  for (int s = 0; s < used; s++) {
+    int rc = ensure_slot(ctx, s, chunk * LIFEB200_PATTERN_BYTES, chunk * sizeof(uint64_t));
+    if (rc) return rc;
+  }
+  for (size_t c = 0; c < nchunks; c++) {
+    Slot& sl = ctx->slots[c % kSlots];
+    const size_t off = c * chunk, cnt = std::min(chunk, n - off);
+    uint64_t* d = static_cast<uint64_t*>(sl.dbuf);
+    uint64_t* dh = static_cast<uint64_t*>(sl.dbuf2);
+    LIFEB200_CUDA(cudaMemcpyAsync(d, patterns + off * kN, cnt * LIFEB200_PATTERN_BYTES, cudaMemcpyHostToDevice, sl.stream));
+    hash_kernel<<<grid_n(cnt, 8), kBlockN, 0, sl.stream>>>(d, dh, cnt);
+    LIFEB200_LAUNCHED(ctx);
+    LIFEB200_CUDA(cudaMemcpyAsync(hashes + off, dh, cnt * sizeof(uint64_t), cudaMemcpyDeviceToHost, sl.stream));
+  }
+  for (int s = 0; s < used; s++) LIFEB200_CUDA(cudaStreamSynchronize(ctx->slots[s].stream));
+  return LIFEB200_OK;
+}
+
+}  // extern "C"

@@ -35,7 +35,7 @@ def aligned_copy(a: np.ndarray, align: int = 64) -> np.ndarray:
 
 
 def build_port(force: bool = False) -> str:
-    srcs = [os.path.join(HERE, f) for f in ("life_oracle.c", "circuits_oracle.c", "stable_oracle.c", "circuit_tables.h")]
+    srcs = [os.path.join(HERE, f) for f in ("life_oracle.c", "circuits_oracle.c", "stable_oracle.c", "next_oracle.c", "circuit_tables.h")]
     if force or not os.path.exists(PORT_SO) or any(os.path.getmtime(s) > os.path.getmtime(PORT_SO) for s in srcs):
         subprocess.run(["make", "-C", HERE, "port"], check=True, stdout=subprocess.DEVNULL)
     return PORT_SO
@@ -119,6 +119,9 @@ class Port:
         _sig(lib, "lo_stable_pass", C.c_uint, [_u64p, C.c_int])
         _sig(lib, "lo_stable_pass_batch", None, [_u64p, C.c_size_t, C.c_int, _u8p, C.c_int])
         _sig(lib, "lo_stable_vulnerable", None, [_u64p, _u64p])
+        _sig(lib, "lo_weld_step_n", None, [_u64p, C.c_uint])
+        _sig(lib, "lo_interaction_counts", None, [_u64p, _u64p])
+        _sig(lib, "lo_xxh3_512", C.c_uint64, [_u64p])
         _sig(lib, "lo_refined_step", None, [_u64p, _u64p, _u64p, C.c_int, _u64p, _u64p, _u64p])
 
     # -- helpers returning fresh arrays ---------------------------------------------------------
@@ -240,6 +243,22 @@ class Port:
             getattr(lib or self.lib, fn)(p[i].reshape(-1), con[i], cun[i], variant, outs[0][i], outs[1][i], outs[2][i])
         return tuple(outs)
 
+    def weld_step(self, records, gens: int, fn="lo_weld_step_n", lib=None):
+        r = aligned_copy(np.asarray(records, dtype=np.uint64).reshape(-1, 4, 64))
+        for i in range(r.shape[0]):
+            getattr(lib or self.lib, fn)(r[i].reshape(-1), gens)
+        return r
+
+    def interaction_counts(self, patterns, fn="lo_interaction_counts", lib=None):
+        p = aligned_copy(np.asarray(patterns, dtype=np.uint64).reshape(-1, 64))
+        out = aligned_copy(np.zeros((p.shape[0], 4, 64), dtype=np.uint64))
+        for i in range(p.shape[0]):
+            getattr(lib or self.lib, fn)(p[i], out[i].reshape(-1))
+        return out
+
+    def hash(self, s) -> int:
+        return self.lib.lo_xxh3_512(np.ascontiguousarray(s, dtype=np.uint64))
+
     def survey(self, first_id, n, seed, dist, gens, cap):
         ids = np.zeros(max(cap, 1), dtype=np.uint64)
         pops = np.zeros(max(cap, 1), dtype=np.uint32)
@@ -292,6 +311,8 @@ class Ref:
         _sig(lib, "ref_stable_pass_batch", None, [_u64p, C.c_size_t, C.c_int, _u8p, C.c_int])
         _sig(lib, "ref_stable_vulnerable", None, [_u64p, _u64p])
         _sig(lib, "ref_zoi_hollow", None, [_u64p, _u64p])
+        _sig(lib, "ref_weld_step_n", None, [_u64p, C.c_uint])
+        _sig(lib, "ref_interaction_counts", None, [_u64p, _u64p])
         _sig(lib, "ref_refined_step", None, [_u64p, _u64p, _u64p, C.c_int, _u64p, _u64p, _u64p])
 
     def isa(self) -> str:
@@ -367,6 +388,12 @@ class Ref:
 
     def stable_vulnerable(self, planes):
         return Port.stable_vulnerable(self, planes, fn="ref_stable_vulnerable", lib=self.lib)
+
+    def weld_step(self, records, gens: int):
+        return Port.weld_step(self, records, gens, fn="ref_weld_step_n", lib=self.lib)
+
+    def interaction_counts(self, patterns):
+        return Port.interaction_counts(self, patterns, fn="ref_interaction_counts", lib=self.lib)
 
     def refined_step(self, planes, cur_on, cur_unk, variant: int):
         return Port.refined_step(self, planes, cur_on, cur_unk, variant, fn="ref_refined_step", lib=self.lib)

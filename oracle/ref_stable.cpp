@@ -114,3 +114,22 @@ extern "C" void ref_refined_step(const uint64_t *planes, const uint64_t *cur_on,
     out_on[i] = next_on; out_unk[i] = next_unknown; out_unk_stable[i] = next_unknown_stable;
   }
 }
+
+// SURVEY.md 8(f) rows through the reference's own members.
+#include "LifeWeld.hpp"
+static_assert(sizeof(LifeWeld) == 2048, "LifeWeld layout");
+extern "C" void ref_weld_step_n(uint64_t *rec, unsigned gens) {
+  LifeWeld w;
+  std::memcpy(static_cast<void *>(&w), rec, sizeof w);
+  for (unsigned g = 0; g < gens; g++) w.Step();
+  std::memcpy(rec, static_cast<const void *>(&w), sizeof w);
+}
+extern "C" void ref_interaction_counts(const uint64_t *s, uint64_t *out) {
+  LifeState st, o1, o2, om, nx, p1, p2, pm;
+  std::memcpy(st.state, s, 512);
+  st.InteractionCountsAndNext(o1, o2, om, nx);
+  st.InteractionCounts(p1, p2, pm);
+  if (!(p1 == o1 && p2 == o2 && pm == om)) std::abort();  // the two members agree on the shared planes
+  std::memcpy(out, o1.state, 512); std::memcpy(out + 64, o2.state, 512);
+  std::memcpy(out + 128, om.state, 512); std::memcpy(out + 192, nx.state, 512);
+}

@@ -20,6 +20,9 @@ void lo_neighbour_count(const uint64_t* s, uint64_t* planes);
 int lo_contains_target(const uint64_t* s, const uint64_t* target);
 unsigned lo_stable_pass(uint64_t* planes, int pass);
 void lo_stable_vulnerable(const uint64_t* planes, uint64_t* out);
+void lo_weld_step_n(uint64_t* rec, unsigned gens);
+void lo_interaction_counts(const uint64_t* s, uint64_t* out);
+uint64_t lo_xxh3_512(const uint64_t* s);
 }
 
 static int failures = 0;
@@ -147,7 +150,37 @@ static void Stable_And_History() {
   EXPECT_EQ(h.history, acc);
 }
 
+// LifeWeld::Step, GetHash, InteractionCountsAndNext through the header.
+static void Weld_Hash_Interaction() {
+  LifeState rp = LifeState::Parse("b2o$2o$bo!");
+  EXPECT_EQ(rp.Stepped(1000).GetHash(), 0xdc35d1573487dc91ULL);  // SURVEY.md 8c known answer
+  std::mt19937_64 rng(5);
+  for (int it = 0; it < 20; it++) {
+    LifeState s = RandomState(rng);
+    EXPECT_EQ(s.GetHash(), lo_xxh3_512(s.state));
+    LifeState o1, o2, om, nx;
+    s.InteractionCountsAndNext(o1, o2, om, nx);
+    uint64_t want[4 * N];
+    lo_interaction_counts(s.state, want);
+    EXPECT_TRUE(std::memcmp(o1.state, want, 512) == 0 && std::memcmp(o2.state, want + N, 512) == 0);
+    EXPECT_TRUE(std::memcmp(om.state, want + 2 * N, 512) == 0 && std::memcmp(nx.state, want + 3 * N, 512) == 0);
+    EXPECT_EQ(nx, s.Stepped());
+    LifeWeld w(s, RandomState(rng) & RandomState(rng) & ~s, RandomState(rng) & RandomState(rng) & ~s, RandomState(rng) & ~s);
+    LifeWeld want_w = w;
+    lo_weld_step_n(reinterpret_cast<uint64_t*>(&want_w), 3);
+    w.Step(3);
+    EXPECT_EQ(w, want_w);
+    LifeWeld plain(s);
+    plain.Step();
+    EXPECT_EQ(plain.state, s.Stepped());  // frozen = 0 is LifeState::Step
+  }
+  // a block welded in place: ToTarget is matched by the weld's own state
+  LifeWeld blk(LifeState::Parse("2o$2o!", 5, 5));
+  EXPECT_TRUE(blk.Contains(blk.ToTarget()));
+}
+
 int main() {
+  Weld_Hash_Interaction();
   Stable_And_History();
   StepAltTest_Random();
   StepN_RPentomino();

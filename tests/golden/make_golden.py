@@ -194,6 +194,20 @@ def main() -> None:
                         refined_on=cur_on, refined_unknown=cur_unk, refined_m=refined[0], refined_old=refined[1])
     print("stable flags per pass:", [np.bincount(f, minlength=4).tolist() for f in flags])
 
+    # ---- 8f next rows: LifeWeld::Step, InteractionCountsAndNext, GetHash --------------------------
+    wsoups = port.soup(7000, 12, SEED, 0)
+    weld = np.zeros((12, 4, 64), dtype=np.uint64)
+    weld[:, 0] = wsoups
+    fr = rng.integers(0, 1 << 63, size=(3, 12, 3, 64), dtype=np.uint64)
+    weld[:8, 1:] = fr[0, :8] & fr[1, :8] & fr[2, :8] & ~wsoups[:8, None, :]  # sparse frozen counts on dead cells
+    wg = [1, 2, 9]
+    np.savez_compressed(os.path.join(OUT, "next_rows.npz"), weld=weld, weld_gens=np.array(wg),
+                        weld_out=np.stack([ref.weld_step(weld, k) for k in wg]),
+                        inter_in=wsoups, inter_out=ref.interaction_counts(wsoups),
+                        hash_in=np.concatenate([wsoups, np.zeros((1, 64), dtype=np.uint64), ~np.zeros((1, 64), dtype=np.uint64)]),
+                        hash_out=np.array([ref.hash(x) for x in np.concatenate(
+                            [wsoups, np.zeros((1, 64), dtype=np.uint64), ~np.zeros((1, 64), dtype=np.uint64)])], dtype=np.uint64))
+
     for f in sorted(os.listdir(OUT)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(OUT, f)), "bytes")

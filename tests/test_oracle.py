@@ -324,3 +324,27 @@ def test_pair_shared_rule_luts_exhaustive():
                     g13 = _lop3(0xF1, co >> 1, g11, g12)
                     n = ca + cb + co
                     assert _lop3(0x94, p8, g12, g13) == int(n == 3 or (cell and n == 4))
+
+
+# ---- 8f next rows ---------------------------------------------------------------------------------
+def test_port_next_rows_golden(port):
+    g = golden("next_rows.npz")
+    for i, k in enumerate(g["weld_gens"]):
+        assert (port.weld_step(g["weld"], int(k)) == g["weld_out"][i]).all()
+    assert (port.interaction_counts(g["inter_in"]) == g["inter_out"]).all()
+    assert [port.hash(x) for x in g["hash_in"]] == [int(h) for h in g["hash_out"]]
+    # XXH3 restatement against the survey's known answers (R-pentomino generations)
+    rp = golden("rpentomino.npz")
+    assert [port.hash(s) for s in rp["states"]] == [int(h) for h in rp["xxh3"]]
+    assert port.hash(golden("soups.npz")["mt1_final"]) == 0x77B09695A0065A59
+
+
+def test_port_vs_reference_next_rows(port, ref):
+    rng = np.random.default_rng(2)
+    s = port.soup(123, 40, SEED, 1)
+    w = np.zeros((40, 4, 64), dtype=np.uint64)
+    w[:, 0] = s
+    w[:, 1:] = rng.integers(0, 1 << 63, size=(40, 3, 64), dtype=np.uint64) << np.uint64(1)  # dense, arbitrary frozen planes
+    assert (port.weld_step(w, 4) == ref.weld_step(w, 4)).all()
+    assert (port.interaction_counts(s) == ref.interaction_counts(s)).all()
+    assert all(port.hash(x) == ref.hash(x) for x in s)
