@@ -197,6 +197,50 @@ int lifeb200_interaction_counts_dev(lifeb200_ctx* ctx, const uint64_t* in, uint6
 int lifeb200_hash_batch_dev(lifeb200_ctx* ctx, const uint64_t* patterns, uint64_t* hashes, size_t n);
 int lifeb200_hash_batch_host(lifeb200_ctx* ctx, const uint64_t* patterns, uint64_t* hashes, size_t n);
 
+/* ---- 8f rank 4: locating patterns on the torus, the step AFTER the stepping path ----------
+ * Operands are plane arrays of 512 B; every count argument (n_a, n_b, n_t, n_targets) is either n
+ * (one operand per problem) or 1 (the same operand for all problems).
+ *
+ * LifeState::Convolve (LifeAPI.hpp:1293-1370): out[p] = a[p].Convolve(b[p]), the torus Minkowski sum
+ * (OR over ON cells (j,k) of a of b.Moved(j,k)). */
+int lifeb200_convolve_batch_dev(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                uint64_t* out, size_t n);
+int lifeb200_convolve_batch_host(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                 uint64_t* out, size_t n);
+/* LifeState::MatchLiveAndDead / MatchLive / Match(const LifeState&) (LifeAPI.hpp:427-442): out[p] has a
+ * cell ON at every offset where `live` fits inside states[p] (and `dead` fits inside its complement).
+ * mode LIFEB200_MATCH_LIVE_AND_DEAD uses both planes; LIFEB200_MATCH_LIVE ignores `dead` (may be NULL);
+ * LIFEB200_MATCH_BOUNDARY takes dead = live.GetBoundary() (LifeAPI.hpp:538), i.e. Match(live). */
+enum { LIFEB200_MATCH_LIVE_AND_DEAD = 0, LIFEB200_MATCH_LIVE = 1, LIFEB200_MATCH_BOUNDARY = 2 };
+int lifeb200_match_batch_dev(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* live,
+                             const uint64_t* dead, size_t n_t, int mode, uint64_t* out);
+int lifeb200_match_batch_host(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* live,
+                              const uint64_t* dead, size_t n_t, int mode, uint64_t* out);
+/* LifeState::Match(const LifeTarget&) (LifeTarget.hpp:53-54); targets are LifeTarget records
+ * {wanted[64], unwanted[64]} = 1024 B (LifeTarget.hpp:5-7). */
+int lifeb200_match_target_batch_dev(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* targets,
+                                    size_t n_targets, uint64_t* out);
+int lifeb200_match_target_batch_host(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* targets,
+                                     size_t n_targets, uint64_t* out);
+/* LifeState::InteractionOffsets (LifeAPI.hpp:1066-1095): out[p] = a[p].InteractionOffsets(b[p]), the
+ * offsets at which b placed on a interacts in the next generation (overlap, birth or overcrowding);
+ * the step BEFORE the stepping path in a search. */
+int lifeb200_interaction_offsets_dev(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                     uint64_t* out, size_t n);
+int lifeb200_interaction_offsets_host(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                      uint64_t* out, size_t n);
+
+/* ---- 8f rank 4: RLE in and out (host functions; strings are a host format) ---------------
+ * LifeState::RLE (Parsing.hpp:8-66,198-202) / LifeHistory::RLE (LifeHistory.hpp:25-44,62-68): writes
+ * the NUL-terminated string into buf (capacity cap) and its length into *len; LIFEB200_E_OVERFLOW
+ * with *len = required length if it does not fit.  LifeState::Parse / LifeHistory::Parse
+ * (Parsing.hpp:141-196, LifeHistory.hpp:70-93): state = 512 B, record = state, history, marked,
+ * original = 2048 B. */
+int lifeb200_rle(const uint64_t* state, char* buf, size_t cap, size_t* len);
+int lifeb200_history_rle(const uint64_t* record, char* buf, size_t cap, size_t* len);
+int lifeb200_parse_rle(const char* rle, uint64_t* state);
+int lifeb200_history_parse_rle(const char* rle, uint64_t* record);
+
 /* ---- roofline denominator: measured LOP3 lane-instructions per second ------------------- */
 int lifeb200_measure_int_peak(lifeb200_ctx* ctx, double* lop3_lane_instr_per_s, double* sm_mhz_effective);
 

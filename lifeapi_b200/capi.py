@@ -90,7 +90,21 @@ SIGNATURES = {
     "lifeb200_hash_batch_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "lifeb200_hash_batch_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "lifeb200_measure_int_peak": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "lifeb200_convolve_batch_dev": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t]),
+    "lifeb200_convolve_batch_host": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t]),
+    "lifeb200_match_batch_dev": (C.c_int, [_vp, _vp, C.c_size_t, _vp, _vp, C.c_size_t, C.c_int, _vp]),
+    "lifeb200_match_batch_host": (C.c_int, [_vp, _vp, C.c_size_t, _vp, _vp, C.c_size_t, C.c_int, _vp]),
+    "lifeb200_match_target_batch_dev": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp]),
+    "lifeb200_match_target_batch_host": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp]),
+    "lifeb200_interaction_offsets_dev": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t]),
+    "lifeb200_interaction_offsets_host": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t]),
+    "lifeb200_rle": (C.c_int, [_vp, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "lifeb200_history_rle": (C.c_int, [_vp, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "lifeb200_parse_rle": (C.c_int, [C.c_char_p, _vp]),
+    "lifeb200_history_parse_rle": (C.c_int, [C.c_char_p, _vp]),
 }
+
+MATCH_LIVE_AND_DEAD, MATCH_LIVE, MATCH_BOUNDARY = 0, 1, 2
 
 
 def declared_functions(header_path: str = HEADER_PATH) -> list[str]:
@@ -438,3 +452,100 @@ class Engine:
         out = np.empty(n, dtype=np.uint64)
         self._check(self.lib.lifeb200_hash_batch_host(self._h, _ptr(patterns), _ptr(out), n))
         return out
+
+    # -- 8f rank 4: Convolve / Match / InteractionOffsets (host arrays through the *_host entry points) ----
+    @staticmethod
+    def _planes(a, words=WORDS):
+        a = np.ascontiguousarray(a, dtype=np.uint64).reshape(-1, words)
+        return a, a.shape[0]
+
+    def convolve_batch_dev(self, d_a, n_a: int, d_b, n_b: int, d_out, n: int) -> None:
+        self._check(self.lib.lifeb200_convolve_batch_dev(self._h, _ptr(d_a), n_a, _ptr(d_b), n_b, _ptr(d_out), n))
+
+    def convolve_batch_host(self, a: np.ndarray, b: np.ndarray) -> np.ndarray:
+        """a, b: (n or 1, 64) planes -> (n, 64); an operand of one plane is shared by all problems."""
+        (a, na), (b, nb) = self._planes(a), self._planes(b)
+        n = max(na, nb)
+        out = np.empty((n, WORDS), dtype=np.uint64)
+        self._check(self.lib.lifeb200_convolve_batch_host(self._h, _ptr(a), na, _ptr(b), nb, _ptr(out), n))
+        return out
+
+    def match_batch_dev(self, d_states, n: int, d_live, d_dead, n_t: int, mode: int, d_out) -> None:
+        self._check(self.lib.lifeb200_match_batch_dev(self._h, _ptr(d_states), n, _ptr(d_live), _ptr(d_dead), n_t, mode, _ptr(d_out)))
+
+    def match_batch_host(self, states: np.ndarray, live: np.ndarray, dead: np.ndarray | None = None,
+                         mode: int = MATCH_LIVE_AND_DEAD) -> np.ndarray:
+        (states, n), (live, nt) = self._planes(states), self._planes(live)
+        if dead is not None:
+            dead, nd = self._planes(dead)
+            if nd != nt:
+                raise ValueError("live / dead counts differ")
+        out = np.empty((n, WORDS), dtype=np.uint64)
+        self._check(self.lib.lifeb200_match_batch_host(self._h, _ptr(states), n, _ptr(live), _ptr(dead), nt, mode, _ptr(out)))
+        return out
+
+    def match_target_batch_dev(self, d_states, n: int, d_targets, n_targets: int, d_out) -> None:
+        self._check(self.lib.lifeb200_match_target_batch_dev(self._h, _ptr(d_states), n, _ptr(d_targets), n_targets, _ptr(d_out)))
+
+    def match_target_batch_host(self, states: np.ndarray, targets: np.ndarray) -> np.ndarray:
+        (states, n), (targets, nt) = self._planes(states), self._planes(targets, 2 * WORDS)
+        out = np.empty((n, WORDS), dtype=np.uint64)
+        self._check(self.lib.lifeb200_match_target_batch_host(self._h, _ptr(states), n, _ptr(targets), nt, _ptr(out)))
+        return out
+
+    def interaction_offsets_dev(self, d_a, n_a: int, d_b, n_b: int, d_out, n: int) -> None:
+        self._check(self.lib.lifeb200_interaction_offsets_dev(self._h, _ptr(d_a), n_a, _ptr(d_b), n_b, _ptr(d_out), n))
+
+    def interaction_offsets_host(self, a: np.ndarray, b: np.ndarray) -> np.ndarray:
+        (a, na), (b, nb) = self._planes(a), self._planes(b)
+        n = max(na, nb)
+        out = np.empty((n, WORDS), dtype=np.uint64)
+        self._check(self.lib.lifeb200_interaction_offsets_host(self._h, _ptr(a), na, _ptr(b), nb, _ptr(out), n))
+        return out
+
+
+# -- 8f rank 4: RLE in and out (host functions of the library; no context, no GPU) --------------------
+def _lib_check(lib, rc: int) -> None:
+    if rc != 0:
+        raise LifeB200Error(rc, lib.lifeb200_last_error().decode())
+
+
+def _rle_call(fn_name: str, planes: np.ndarray) -> str:
+    lib = load_library()
+    planes = np.ascontiguousarray(planes, dtype=np.uint64)
+    cap = 1 << 12
+    while True:
+        buf = C.create_string_buffer(cap)
+        n = C.c_size_t()
+        rc = getattr(lib, fn_name)(_ptr(planes), buf, cap, C.byref(n))
+        if rc == E_OVERFLOW:
+            cap = n.value + 1
+            continue
+        _lib_check(lib, rc)
+        return buf.value.decode()
+
+
+def rle(state: np.ndarray) -> str:
+    """LifeState::RLE()."""
+    return _rle_call("lifeb200_rle", state)
+
+
+def history_rle(record: np.ndarray) -> str:
+    """LifeHistory::RLE() of a (4, 64) record: state, history, marked, original."""
+    return _rle_call("lifeb200_history_rle", record)
+
+
+def parse_rle(text: str) -> np.ndarray:
+    """LifeState::Parse()."""
+    lib = load_library()
+    out = np.zeros(WORDS, dtype=np.uint64)
+    _lib_check(lib, lib.lifeb200_parse_rle(text.encode(), _ptr(out)))
+    return out
+
+
+def history_parse_rle(text: str) -> np.ndarray:
+    """LifeHistory::Parse() -> (4, 64) record."""
+    lib = load_library()
+    out = np.zeros((4, WORDS), dtype=np.uint64)
+    _lib_check(lib, lib.lifeb200_history_parse_rle(text.encode(), _ptr(out)))
+    return out

@@ -1,0 +1,313 @@
+// convolve.cu -- the step AFTER the stepping path: locating patterns on the torus.
+//   LifeState::Convolve            LifeAPI.hpp:1293-1370 (+ Bits.hpp:132-143)
+//   MatchLive / MatchLiveAndDead   LifeAPI.hpp:427-435;  Match(LifeState) :440-442;  Match(LifeTarget) LifeTarget.hpp:53-54
+//   LifeState::InteractionOffsets  LifeAPI.hpp:1066-1095
+//   LifeState::Mirrored            LifeAPI.hpp:789-795
+// One warp owns one problem: lane L keeps words 2L and 2L+1 of every plane.  Convolve is the torus
+// Minkowski sum  result = OR over ON cells (j,k) of X of Y.Moved(j,k); it is commutative, so the warp
+// walks whichever operand has fewer ON cells.  The walk is warp-uniform (the walked word is broadcast
+// with a shuffle, every lane takes the same branches): empty columns are skipped with one ballot,
+// and a run of r consecutive ON bits costs O(log r) rotate-ORs (the doubling the reference applies to
+// runs, LifeAPI.hpp:1309-1366) instead of r.  The shifted operand's column j arrives by shuffle from
+// lane L - j/2, so nothing touches shared or global memory between the load and the store.
+#include <algorithm>
+
+#include "ctx.h"
+#include "life_core.cuh"
+
+namespace lifeb200 {
+
+constexpr int kBlockC = 256;
+constexpr unsigned kFull = 0xffffffffu;
+static inline unsigned grid_warps(size_t n) { return (unsigned)((n * 32 + kBlockC - 1) / kBlockC); }
+
+struct Plane {
+  uint64_t w0, w1;  // words 2L, 2L+1 of this lane
+};
+
+__device__ __forceinline__ uint64_t rotl64(uint64_t v, int s) { return (v << (s & 63)) | (v >> ((64 - s) & 63)); }
+__device__ __forceinline__ uint64_t shfl64(uint64_t v, int src) { return __shfl_sync(kFull, v, src & 31); }
+
+__device__ __forceinline__ Plane load_plane(const uint64_t* __restrict__ p, int lane) {
+  const uint4 v = __ldg(reinterpret_cast<const uint4*>(p) + lane);
+  Plane r;
+  r.w0 = ((uint64_t)v.y << 32) | v.x;
+  r.w1 = ((uint64_t)v.w << 32) | v.z;
+  return r;
+}
+__device__ __forceinline__ void store_plane(uint64_t* __restrict__ p, int lane, const Plane& r) {
+  reinterpret_cast<uint4*>(p)[lane] = make_uint4((uint32_t)r.w0, (uint32_t)(r.w0 >> 32), (uint32_t)r.w1, (uint32_t)(r.w1 >> 32));
+}
+__device__ __forceinline__ Plane zero_plane() { Plane r; r.w0 = r.w1 = 0; return r; }
+__device__ __forceinline__ Plane operator~(const Plane& a) { Plane r; r.w0 = ~a.w0; r.w1 = ~a.w1; return r; }
+__device__ __forceinline__ Plane operator&(const Plane& a, const Plane& b) { Plane r; r.w0 = a.w0 & b.w0; r.w1 = a.w1 & b.w1; return r; }
+__device__ __forceinline__ Plane operator|(const Plane& a, const Plane& b) { Plane r; r.w0 = a.w0 | b.w0; r.w1 = a.w1 | b.w1; return r; }
+
+__device__ __forceinline__ unsigned warp_pop(const Plane& a) {
+  unsigned p = __popcll(a.w0) + __popcll(a.w1);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) p += __shfl_xor_sync(kFull, p, o);
+  return p;
+}
+
+// (x, y) -> (-x, -y): word i = rotl(brev(s[(64 - i) & 63]), 1)   (FlipX, FlipY, Move(1,1))
+__device__ __forceinline__ Plane mirrored(const Plane& s, int lane) {
+  Plane r;
+  r.w0 = rotl64(__brevll(shfl64(s.w0, 32 - lane)), 1);  // word (64 - 2L) & 63 = word 0 of lane (32 - L) & 31
+  r.w1 = rotl64(__brevll(shfl64(s.w1, 31 - lane)), 1);  // word 63 - 2L = word 1 of lane 31 - L
+  return r;
+}
+
+// acc |= OR over ON bits k of x of rotl(y, k), for this lane's two result words (x is warp-uniform)
+__device__ __forceinline__ void spread(uint64_t x, uint64_t y0, uint64_t y1, Plane& acc) {
+  while (x) {
+    const int k = __ffsll((long long)x) - 1;
+    const uint64_t sh = x >> k;
+    const int r = (~sh == 0) ? 64 : __ffsll((long long)~sh) - 1;  // run length starting at bit k
+    uint64_t t0 = y0, t1 = y1;
+    int s = 1;
+    while (2 * s <= r) { t0 |= rotl64(t0, s); t1 |= rotl64(t1, s); s *= 2; }
+    if (r > s) { t0 |= rotl64(t0, r - s); t1 |= rotl64(t1, r - s); }
+    acc.w0 |= rotl64(t0, k);
+    acc.w1 |= rotl64(t1, k);
+    x = (r == 64) ? 0 : x & ~(((1ULL << r) - 1) << k);
+  }
+}
+
+// acc |= X (*) Y, walking X
+__device__ __forceinline__ void conv_walk(const Plane& x, const Plane& y, Plane& acc, int lane) {
+  unsigned nz0 = __ballot_sync(kFull, x.w0 != 0);  // columns 2*lane
+  unsigned nz1 = __ballot_sync(kFull, x.w1 != 0);  // columns 2*lane + 1
+  while (nz0) {
+    const int jj = __ffs(nz0) - 1;
+    nz0 &= nz0 - 1;
+    const uint64_t xa = shfl64(x.w0, jj);  // column j = 2jj: result words 2L, 2L+1 take y[2L-2jj], y[2L+1-2jj]
+    spread(xa, shfl64(y.w0, lane - jj), shfl64(y.w1, lane - jj), acc);
+  }
+  while (nz1) {
+    const int jj = __ffs(nz1) - 1;
+    nz1 &= nz1 - 1;
+    const uint64_t xb = shfl64(x.w1, jj);  // column j = 2jj+1: y[2L-2jj-1], y[2L-2jj]
+    spread(xb, shfl64(y.w1, lane - jj - 1), shfl64(y.w0, lane - jj), acc);
+  }
+}
+
+__device__ __forceinline__ Plane convolve(const Plane& a, const Plane& b, int lane) {
+  Plane acc = zero_plane();
+  if (warp_pop(a) <= warp_pop(b)) conv_walk(a, b, acc, lane);
+  else conv_walk(b, a, acc, lane);
+  return acc;
+}
+
+__device__ __forceinline__ Plane to_plane(const Tile<32>& t) {
+  Plane r;
+  r.w0 = ((uint64_t)t.hi[0] << 32) | t.lo[0];
+  r.w1 = ((uint64_t)t.hi[1] << 32) | t.lo[1];
+  return r;
+}
+__device__ __forceinline__ Tile<32> to_tile(const Plane& p) {
+  Tile<32> t;
+  t.lo[0] = (uint32_t)p.w0; t.hi[0] = (uint32_t)(p.w0 >> 32);
+  t.lo[1] = (uint32_t)p.w1; t.hi[1] = (uint32_t)(p.w1 >> 32);
+  return t;
+}
+
+__global__ void __launch_bounds__(kBlockC) convolve_kernel(const uint64_t* __restrict__ a, size_t n_a,
+                                                           const uint64_t* __restrict__ b, size_t n_b,
+                                                           uint64_t* __restrict__ out, size_t n) {
+  const size_t p = ((size_t)blockIdx.x * kBlockC + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (p >= n) return;  // whole warps leave together
+  const Plane A = load_plane(a + (n_a == 1 ? 0 : p) * kN, lane);
+  const Plane B = load_plane(b + (n_b == 1 ? 0 : p) * kN, lane);
+  store_plane(out + p * kN, lane, convolve(A, B, lane));
+}
+
+// mode 0: live + dead planes given; 1: live only (MatchLive); 2: dead = live.GetBoundary() (Match(LifeState))
+__global__ void __launch_bounds__(kBlockC) match_kernel(const uint64_t* __restrict__ states, size_t n,
+                                                        const uint64_t* __restrict__ live, const uint64_t* __restrict__ dead,
+                                                        size_t n_t, size_t t_stride, int mode, uint64_t* __restrict__ out) {
+  const size_t p = ((size_t)blockIdx.x * kBlockC + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (p >= n) return;
+  const size_t ti = (n_t == 1 ? 0 : p) * t_stride;
+  const Plane S = load_plane(states + p * kN, lane);
+  const Plane L = load_plane(live + ti, lane);
+  // ~((~this).Convolve(live.Mirrored()))
+  Plane r = ~convolve(~S, mirrored(L, lane), lane);
+  if (mode != 1) {
+    Plane D;
+    if (mode == 0) D = load_plane(dead + ti, lane);
+    else D = to_plane(dilate<32>(to_tile(L), lane, false)) & ~L;  // ZOI() & ~live (LifeAPI.hpp:538)
+    r = r & ~convolve(S, mirrored(D, lane), lane);
+  }
+  store_plane(out + p * kN, lane, r);
+}
+
+__global__ void __launch_bounds__(kBlockC) interaction_offsets_kernel(const uint64_t* __restrict__ a, size_t n_a,
+                                                                      const uint64_t* __restrict__ b, size_t n_b,
+                                                                      uint64_t* __restrict__ out, size_t n) {
+  const size_t p = ((size_t)blockIdx.x * kBlockC + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (p >= n) return;
+  const Plane A = load_plane(a + (n_a == 1 ? 0 : p) * kN, lane);
+  const Plane B = mirrored(load_plane(b + (n_b == 1 ? 0 : p) * kN, lane), lane);
+  Tile<32> t3, t2, t1, t0;
+  to_tile(A).neighbour_count(lane, t3, t2, t1, t0);
+  const Plane a3 = to_plane(t3), a2 = to_plane(t2), a1 = to_plane(t1), a0 = to_plane(t0);
+  to_tile(B).neighbour_count(lane, t3, t2, t1, t0);
+  const Plane b3 = to_plane(t3), b2 = to_plane(t2), b1 = to_plane(t1), b0 = to_plane(t0);
+  const Plane a_lo = ~a3 & ~a2, b_lo = ~b3 & ~b2;  // count < 4
+  Plane r = convolve(A, B, lane);                                                  // overlaps
+  r = r | convolve(a_lo & ~a1 & a0 & ~A, b_lo & b1 & ~b0 & ~B, lane);              // births: 1 next to 2
+  r = r | convolve(b_lo & ~b1 & b0 & ~B, a_lo & a1 & ~a0 & ~A, lane);
+  r = r | convolve(a_lo & a1 & a0 & A, (b3 | b2 | b1) & ~B, lane);                 // overcrowding
+  r = r | convolve((a2 | a3) & A, (b3 | b2 | b1 | b0) & ~B, lane);
+  r = r | convolve(b_lo & b1 & b0 & B, (a3 | a2 | a1) & ~A, lane);
+  r = r | convolve((b2 | b3) & B, (a3 | a2 | a1 | a0) & ~A, lane);
+  store_plane(out + p * kN, lane, r);
+}
+
+// ---- host-pointer variants: up to three plane inputs, each either per-problem or broadcast ----
+struct HostIn {
+  const uint64_t* ptr;
+  size_t count;   // 1 (broadcast) or n
+  size_t words;   // words per item (64, or 128 for interleaved LifeTarget records)
+};
+
+template <class LaunchFn>
+int planes_host(lifeb200_ctx* ctx, const HostIn* ins, int n_ins, uint64_t* out, size_t n, LaunchFn launch) {
+  const size_t chunk = std::min<size_t>(n, (size_t)1 << 15);
+  const size_t nchunks = (n + chunk - 1) / chunk;
+  const int used = (int)std::min<size_t>(kSlots, nchunks);
+  size_t in_bytes = 0;
+  for (int i = 0; i < n_ins; i++) in_bytes += (ins[i].count == 1 ? 1 : chunk) * ins[i].words * 8;
+  for (int s = 0; s < used; s++) {
+    int rc = ensure_slot(ctx, s, in_bytes, chunk * LIFEB200_PATTERN_BYTES);
+    if (rc) return rc;
+  }
+  for (size_t c = 0; c < nchunks; c++) {
+    Slot& sl = ctx->slots[c % kSlots];
+    const size_t off = c * chunk, cnt = std::min(chunk, n - off);
+    const uint64_t* dptr[3] = {nullptr, nullptr, nullptr};
+    uint64_t* d = static_cast<uint64_t*>(sl.dbuf);
+    for (int i = 0; i < n_ins; i++) {
+      if (!ins[i].ptr) continue;
+      const bool bc = ins[i].count == 1;
+      const size_t items = bc ? 1 : cnt;
+      LIFEB200_CUDA(cudaMemcpyAsync(d, ins[i].ptr + (bc ? 0 : off * ins[i].words), items * ins[i].words * 8,
+                                    cudaMemcpyHostToDevice, sl.stream));
+      dptr[i] = d;
+      d += (bc ? 1 : chunk) * ins[i].words;
+    }
+    uint64_t* dout = static_cast<uint64_t*>(sl.dbuf2);
+    launch(dptr, dout, cnt, sl.stream);
+    LIFEB200_LAUNCHED(ctx);
+    LIFEB200_CUDA(cudaMemcpyAsync(out + off * kN, dout, cnt * LIFEB200_PATTERN_BYTES, cudaMemcpyDeviceToHost, sl.stream));
+  }
+  for (int s = 0; s < used; s++) LIFEB200_CUDA(cudaStreamSynchronize(ctx->slots[s].stream));
+  return LIFEB200_OK;
+}
+
+static int check_pair(const void* a, size_t n_a, const void* b, size_t n_b, const void* out, size_t n, bool need_align) {
+  if (!a || !b || !out) return set_error(LIFEB200_E_ARG, "null pointer");
+  if ((n_a != 1 && n_a != n) || (n_b != 1 && n_b != n)) return set_error(LIFEB200_E_ARG, "operand counts must be 1 (broadcast) or n");
+  if (need_align && (!aligned16(a) || !aligned16(b) || !aligned16(out))) return set_error(LIFEB200_E_ARG, "misaligned device pointer");
+  return LIFEB200_OK;
+}
+
+}  // namespace lifeb200
+
+using namespace lifeb200;
+
+extern "C" {
+
+int lifeb200_convolve_batch_dev(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                uint64_t* out, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (int rc = check_pair(a, n_a, b, n_b, out, n, true)) return rc;
+  convolve_kernel<<<grid_warps(n), kBlockC, 0, ctx->stream>>>(a, n_a, b, n_b, out, n);
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+int lifeb200_convolve_batch_host(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                 uint64_t* out, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (int rc = check_pair(a, n_a, b, n_b, out, n, false)) return rc;
+  const HostIn ins[2] = {{a, n_a, (size_t)kN}, {b, n_b, (size_t)kN}};
+  return planes_host(ctx, ins, 2, out, n, [&](const uint64_t* const* d, uint64_t* dout, size_t cnt, cudaStream_t st) {
+    convolve_kernel<<<grid_warps(cnt), kBlockC, 0, st>>>(d[0], n_a == 1 ? 1 : cnt, d[1], n_b == 1 ? 1 : cnt, dout, cnt);
+  });
+}
+
+int lifeb200_match_batch_dev(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* live,
+                             const uint64_t* dead, size_t n_t, int mode, uint64_t* out) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (mode < 0 || mode > 2) return set_error(LIFEB200_E_ARG, "match mode must be 0, 1 or 2");
+  if (int rc = check_pair(states, n, live, n_t, out, n, true)) return rc;
+  if (mode == 0 && (!dead || !aligned16(dead))) return set_error(LIFEB200_E_ARG, "mode 0 needs a dead plane");
+  match_kernel<<<grid_warps(n), kBlockC, 0, ctx->stream>>>(states, n, live, dead, n_t, kN, mode, out);
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+int lifeb200_match_batch_host(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* live,
+                              const uint64_t* dead, size_t n_t, int mode, uint64_t* out) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (mode < 0 || mode > 2) return set_error(LIFEB200_E_ARG, "match mode must be 0, 1 or 2");
+  if (int rc = check_pair(states, n, live, n_t, out, n, false)) return rc;
+  if (mode == 0 && !dead) return set_error(LIFEB200_E_ARG, "mode 0 needs a dead plane");
+  const HostIn ins[3] = {{states, n, (size_t)kN}, {live, n_t, (size_t)kN}, {mode == 0 ? dead : nullptr, n_t, (size_t)kN}};
+  return planes_host(ctx, ins, 3, out, n, [&](const uint64_t* const* d, uint64_t* dout, size_t cnt, cudaStream_t st) {
+    match_kernel<<<grid_warps(cnt), kBlockC, 0, st>>>(d[0], cnt, d[1], d[2], n_t == 1 ? 1 : cnt, kN, mode, dout);
+  });
+}
+
+int lifeb200_match_target_batch_dev(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* targets,
+                                    size_t n_targets, uint64_t* out) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (int rc = check_pair(states, n, targets, n_targets, out, n, true)) return rc;
+  match_kernel<<<grid_warps(n), kBlockC, 0, ctx->stream>>>(states, n, targets, targets + kN, n_targets, 2 * kN, 0, out);
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+int lifeb200_match_target_batch_host(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* targets,
+                                     size_t n_targets, uint64_t* out) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (int rc = check_pair(states, n, targets, n_targets, out, n, false)) return rc;
+  const HostIn ins[2] = {{states, n, (size_t)kN}, {targets, n_targets, (size_t)(2 * kN)}};
+  return planes_host(ctx, ins, 2, out, n, [&](const uint64_t* const* d, uint64_t* dout, size_t cnt, cudaStream_t st) {
+    match_kernel<<<grid_warps(cnt), kBlockC, 0, st>>>(d[0], cnt, d[1], d[1] + kN, n_targets == 1 ? 1 : cnt, 2 * kN, 0, dout);
+  });
+}
+
+int lifeb200_interaction_offsets_dev(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                     uint64_t* out, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (int rc = check_pair(a, n_a, b, n_b, out, n, true)) return rc;
+  interaction_offsets_kernel<<<grid_warps(n), kBlockC, 0, ctx->stream>>>(a, n_a, b, n_b, out, n);
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+int lifeb200_interaction_offsets_host(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                      uint64_t* out, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (int rc = check_pair(a, n_a, b, n_b, out, n, false)) return rc;
+  const HostIn ins[2] = {{a, n_a, (size_t)kN}, {b, n_b, (size_t)kN}};
+  return planes_host(ctx, ins, 2, out, n, [&](const uint64_t* const* d, uint64_t* dout, size_t cnt, cudaStream_t st) {
+    interaction_offsets_kernel<<<grid_warps(cnt), kBlockC, 0, st>>>(d[0], n_a == 1 ? 1 : cnt, d[1], n_b == 1 ? 1 : cnt, dout, cnt);
+  });
+}
+
+}  // extern "C"

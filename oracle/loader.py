@@ -35,7 +35,7 @@ def aligned_copy(a: np.ndarray, align: int = 64) -> np.ndarray:
 
 
 def build_port(force: bool = False) -> str:
-    srcs = [os.path.join(HERE, f) for f in ("life_oracle.c", "circuits_oracle.c", "stable_oracle.c", "next_oracle.c", "circuit_tables.h")]
+    srcs = [os.path.join(HERE, f) for f in ("life_oracle.c", "circuits_oracle.c", "stable_oracle.c", "next_oracle.c", "convolve_oracle.c", "circuit_tables.h")]
     if force or not os.path.exists(PORT_SO) or any(os.path.getmtime(s) > os.path.getmtime(PORT_SO) for s in srcs):
         subprocess.run(["make", "-C", HERE, "port"], check=True, stdout=subprocess.DEVNULL)
     return PORT_SO
@@ -123,6 +123,62 @@ class Port:
         _sig(lib, "lo_interaction_counts", None, [_u64p, _u64p])
         _sig(lib, "lo_xxh3_512", C.c_uint64, [_u64p])
         _sig(lib, "lo_refined_step", None, [_u64p, _u64p, _u64p, C.c_int, _u64p, _u64p, _u64p])
+        _sig(lib, "lo_mirrored", None, [_u64p, _u64p])
+        _sig(lib, "lo_convolve", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "lo_match_live", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "lo_match_live_and_dead", None, [_u64p, _u64p, _u64p, _u64p])
+        _sig(lib, "lo_match_state", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "lo_match_target", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "lo_interaction_offsets", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "lo_rle", C.c_size_t, [_u64p, C.c_char_p, C.c_size_t])
+        _sig(lib, "lo_history_rle", C.c_size_t, [_u64p, C.c_char_p, C.c_size_t])
+        _sig(lib, "lo_parse", None, [C.c_char_p, _u64p])
+
+    # -- Convolve / Match / InteractionOffsets / RLE -------------------------
+    _PFX = "lo_"
+
+    def _plane_fn(self, name, *planes):
+        out = np.empty(64, dtype=np.uint64)
+        getattr(self.lib, self._PFX + name)(*[np.ascontiguousarray(p, dtype=np.uint64).reshape(-1) for p in planes], out)
+        return out
+
+    def mirrored(self, s):
+        return self._plane_fn("mirrored", s)
+
+    def convolve(self, a, b):
+        return self._plane_fn("convolve", a, b)
+
+    def match_live(self, s, live):
+        return self._plane_fn("match_live", s, live)
+
+    def match_live_and_dead(self, s, live, dead):
+        return self._plane_fn("match_live_and_dead", s, live, dead)
+
+    def match_state(self, s, live):
+        return self._plane_fn("match_state", s, live)
+
+    def match_target(self, s, target):
+        return self._plane_fn("match_target", s, target)
+
+    def interaction_offsets(self, a, b):
+        return self._plane_fn("interaction_offsets", a, b)
+
+    def _rle(self, name, planes) -> str:
+        buf = C.create_string_buffer(1 << 16)
+        n = getattr(self.lib, self._PFX + name)(np.ascontiguousarray(planes, dtype=np.uint64).reshape(-1), buf, len(buf))
+        assert n < len(buf)
+        return buf.value.decode()
+
+    def rle(self, s) -> str:
+        return self._rle("rle", s)
+
+    def history_rle(self, rec) -> str:
+        return self._rle("history_rle", rec)
+
+    def parse(self, rle: str, dx: int = 0, dy: int = 0) -> np.ndarray:
+        out = np.empty(64, dtype=np.uint64)
+        self.lib.lo_parse(rle.encode(), out)
+        return self.moved(out, dx, dy) if (dx or dy) else out
 
     # -- helpers returning fresh arrays ---------------------------------------------------------
     def threads(self) -> int:
@@ -314,6 +370,48 @@ class Ref:
         _sig(lib, "ref_weld_step_n", None, [_u64p, C.c_uint])
         _sig(lib, "ref_interaction_counts", None, [_u64p, _u64p])
         _sig(lib, "ref_refined_step", None, [_u64p, _u64p, _u64p, C.c_int, _u64p, _u64p, _u64p])
+        _sig(lib, "ref_mirrored", None, [_u64p, _u64p])
+        _sig(lib, "ref_convolve", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "ref_match_live", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "ref_match_live_and_dead", None, [_u64p, _u64p, _u64p, _u64p])
+        _sig(lib, "ref_match_state", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "ref_match_target", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "ref_interaction_offsets", None, [_u64p, _u64p, _u64p])
+        _sig(lib, "ref_rle", C.c_size_t, [_u64p, C.c_char_p, C.c_size_t])
+        _sig(lib, "ref_history_rle", C.c_size_t, [_u64p, C.c_char_p, C.c_size_t])
+        _sig(lib, "ref_history_parse", None, [C.c_char_p, _u64p])
+        _sig(lib, "ref_match_target_batch", None, [_u64p, C.c_size_t, _u64p, _u64p, C.c_int])
+        _sig(lib, "ref_interaction_offsets_batch", None, [_u64p, _u64p, C.c_size_t, _u64p, C.c_int])
+
+    _PFX = "ref_"
+    _plane_fn = Port._plane_fn
+    mirrored = Port.mirrored
+    convolve = Port.convolve
+    match_live = Port.match_live
+    match_live_and_dead = Port.match_live_and_dead
+    match_state = Port.match_state
+    match_target = Port.match_target
+    interaction_offsets = Port.interaction_offsets
+    _rle = Port._rle
+    rle = Port.rle
+    history_rle = Port.history_rle
+
+    def history_parse(self, rle: str) -> np.ndarray:
+        out = np.empty((4, 64), dtype=np.uint64)
+        self.lib.ref_history_parse(rle.encode(), out.reshape(-1))
+        return out
+
+    def match_target_batch(self, states, target, threads: int = 0) -> np.ndarray:
+        st = aligned_copy(np.asarray(states, dtype=np.uint64).reshape(-1, 64))
+        out = aligned_copy(np.zeros_like(st))
+        self.lib.ref_match_target_batch(st.reshape(-1), st.shape[0], aligned_copy(np.asarray(target).reshape(-1)), out.reshape(-1), threads)
+        return out
+
+    def interaction_offsets_batch(self, a, bs, threads: int = 0) -> np.ndarray:
+        b = aligned_copy(np.asarray(bs, dtype=np.uint64).reshape(-1, 64))
+        out = aligned_copy(np.zeros_like(b))
+        self.lib.ref_interaction_offsets_batch(aligned_copy(np.asarray(a).reshape(-1)), b.reshape(-1), b.shape[0], out.reshape(-1), threads)
+        return out
 
     def isa(self) -> str:
         return self.lib.ref_isa().decode()

@@ -143,4 +143,56 @@ int ref_step_match(uint64_t *s, const uint64_t *target, unsigned gens, unsigned 
   return hit;
 }
 
+// ---- Convolve / Match / InteractionOffsets / RLE, the reference's own members ----
+void ref_mirrored(const uint64_t *s, uint64_t *out) { store(load(s).Mirrored(), out); }
+void ref_convolve(const uint64_t *a, const uint64_t *b, uint64_t *out) { store(load(a).Convolve(load(b)), out); }
+void ref_match_live(const uint64_t *s, const uint64_t *live, uint64_t *out) { store(load(s).MatchLive(load(live)), out); }
+void ref_match_live_and_dead(const uint64_t *s, const uint64_t *live, const uint64_t *dead, uint64_t *out) {
+  store(load(s).MatchLiveAndDead(load(live), load(dead)), out);
+}
+void ref_match_state(const uint64_t *s, const uint64_t *live, uint64_t *out) { store(load(s).Match(load(live)), out); }
+void ref_match_target(const uint64_t *s, const uint64_t *target, uint64_t *out) {
+  LifeTarget t;
+  std::memcpy(&t, target, 1024);
+  store(load(s).Match(t), out);
+}
+void ref_interaction_offsets(const uint64_t *a, const uint64_t *b, uint64_t *out) {
+  store(load(a).InteractionOffsets(load(b)), out);
+}
+static size_t copy_out(const std::string &r, char *buf, size_t cap) {
+  if (cap) { size_t k = r.size() < cap - 1 ? r.size() : cap - 1; std::memcpy(buf, r.data(), k); buf[k] = 0; }
+  return r.size();
+}
+size_t ref_rle(const uint64_t *s, char *buf, size_t cap) { return copy_out(load(s).RLE(), buf, cap); }
+size_t ref_history_rle(const uint64_t *rec, char *buf, size_t cap) {
+  LifeHistory h(load(rec), load(rec + 64), load(rec + 128), load(rec + 192));
+  return copy_out(h.RLE(), buf, cap);
+}
+void ref_history_parse(const char *rle, uint64_t *rec) {
+  LifeHistory h = LifeHistory::Parse(rle);
+  store(h.state, rec); store(h.history, rec + 64); store(h.marked, rec + 128); store(h.original, rec + 192);
+}
+// batch timing helpers for bench_extras (CPU baseline of the same rows), contiguous chunks over threads
+void ref_match_target_batch(const uint64_t *states, size_t n, const uint64_t *target, uint64_t *out, int threads) {
+  LifeTarget t;
+  std::memcpy(&t, target, 1024);
+  if (threads <= 0) threads = (int)std::thread::hardware_concurrency();
+  std::vector<std::thread> pool;
+  for (int k = 0; k < threads; k++) {
+    size_t lo = n * k / threads, hi = n * (k + 1) / threads;
+    pool.emplace_back([=] { for (size_t i = lo; i < hi; i++) store(load(states + 64 * i).Match(t), out + 64 * i); });
+  }
+  for (auto &th : pool) th.join();
+}
+void ref_interaction_offsets_batch(const uint64_t *a, const uint64_t *b, size_t n, uint64_t *out, int threads) {
+  if (threads <= 0) threads = (int)std::thread::hardware_concurrency();
+  std::vector<std::thread> pool;
+  LifeState as = load(a);
+  for (int k = 0; k < threads; k++) {
+    size_t lo = n * k / threads, hi = n * (k + 1) / threads;
+    pool.emplace_back([=] { for (size_t i = lo; i < hi; i++) store(as.InteractionOffsets(load(b + 64 * i)), out + 64 * i); });
+  }
+  for (auto &th : pool) th.join();
+}
+
 }  // extern "C"

@@ -90,11 +90,77 @@ def unknown_free_noise(rng, n: int) -> np.ndarray:
     return out
 
 
+def density_planes(rng, n: int, density_log2: int) -> np.ndarray:
+    """n random planes with cell density 2^-density_log2 (AND of independent random words)."""
+    out = rng.integers(0, 1 << 63, size=(n, 64), dtype=np.uint64) << np.uint64(1) | rng.integers(0, 2, size=(n, 64), dtype=np.uint64)
+    for _ in range(density_log2 - 1):
+        out &= rng.integers(0, 1 << 63, size=(n, 64), dtype=np.uint64) << np.uint64(1) | rng.integers(0, 2, size=(n, 64), dtype=np.uint64)
+    return out
+
+
+def locate_inputs(ref: Ref, port: Port):
+    """Operand pairs for Convolve / Match / InteractionOffsets: random planes of several densities, full and
+    empty planes, runs that wrap around bit 63 -> 0, and real objects (catalysts, gliders) placed on soups."""
+    rng = np.random.default_rng(777)
+    cats = np.stack([ref.parse(r, 28, 28) for r in CATALYSTS.values()])
+    gl = glider_variants(ref)
+    a = [density_planes(rng, 4, 6), density_planes(rng, 4, 1), density_planes(rng, 3, 3), cats[:4]]
+    b = [density_planes(rng, 4, 7), density_planes(rng, 4, 5), density_planes(rng, 3, 1), gl[[0, 5, 18, 31]]]
+    a, b = np.concatenate(a), np.concatenate(b)
+    full, empty = ~np.zeros((1, 64), dtype=np.uint64), np.zeros((1, 64), dtype=np.uint64)
+    wrap = np.zeros((1, 64), dtype=np.uint64)
+    wrap[0, 0] = np.uint64(0xF00000000000000F)   # a run of ON bits through the 63 -> 0 seam
+    wrap[0, 63] = np.uint64(0x8000000000000001)
+    wrap[0, 31] = np.uint64(0x00FFFFFFFFFFFF00)  # a run longer than 32 (the reference caps runs at 32)
+    a = np.concatenate([a, full, empty, wrap, full, wrap])
+    b = np.concatenate([b, gl[:1], cats[:1], cats[1:2], full, wrap])
+    # states that really contain the objects looked for: a soup with catalysts pasted in at known offsets
+    states = density_planes(rng, 8, 3)
+    live = cats[:8].copy()
+    for i in range(8):
+        dx, dy = int(rng.integers(64)), int(rng.integers(64))
+        zone = ref.zoi(ref.moved(cats[i], dx, dy))
+        states[i] = (states[i] & ~zone) | ref.moved(cats[i], dx, dy)
+    return a, b, states, live
+
+
+def make_locate(ref: Ref, port: Port) -> None:
+    a, b, states, live = locate_inputs(ref, port)
+    rng = np.random.default_rng(778)
+    dead = np.stack([ref.zoi(x) & ~x for x in live])
+    dead[::2] &= density_planes(rng, 4, 1)  # partial dead masks as well as the full boundary
+    targets = np.stack([np.concatenate([l, d]) for l, d in zip(live, dead)])
+    hist = np.stack([np.stack([states[i], states[i] | a[i], density_planes(rng, 1, 4)[0], density_planes(rng, 1, 6)[0]])
+                     for i in range(4)])
+    rle_in = np.concatenate([a[[0, 4, 11, 15, 16, 17]], states[:2]])
+    np.savez_compressed(
+        os.path.join(OUT, "locate.npz"), a=a, b=b,
+        mirrored=np.stack([ref.mirrored(x) for x in a]),
+        convolve=np.stack([ref.convolve(x, y) for x, y in zip(a, b)]),
+        convolve_bcast=np.stack([ref.convolve(a[0], y) for y in b]),
+        offsets=np.stack([ref.interaction_offsets(x, y) for x, y in zip(a, b)]),
+        offsets_bcast=np.stack([ref.interaction_offsets(a[11], y) for y in b]),
+        states=states, live=live, dead=dead, targets=targets,
+        match_live=np.stack([ref.match_live(s, l) for s, l in zip(states, live)]),
+        match_live_and_dead=np.stack([ref.match_live_and_dead(s, l, d) for s, l, d in zip(states, live, dead)]),
+        match_state=np.stack([ref.match_state(s, l) for s, l in zip(states, live)]),
+        match_target=np.stack([ref.match_target(s, t) for s, t in zip(states, targets)]),
+        match_state_bcast=np.stack([ref.match_state(s, live[0]) for s in states]),
+        match_on_ab=np.stack([ref.match_live_and_dead(x, y, ref.mirrored(y)) for x, y in zip(a, b)]),
+        rle_in=rle_in, rle=np.array([ref.rle(x) for x in rle_in]),
+        history_in=hist, history_rle=np.array([ref.history_rle(h) for h in hist]))
+    found = [int(ref.pop(m)) for m in np.stack([ref.match_state(s, l) for s, l in zip(states, live)])]
+    print("locate: Match(live) offsets found per state:", found)
+
+
 def main() -> None:
     build_ref()
     ref = Ref.load()
     assert ref is not None, "oracle/_ref missing"
     port = Port()
+    if sys.argv[1:] == ["locate"]:  # only the 8f rank-4 vectors (the others are unchanged)
+        make_locate(ref, port)
+        return
 
     # ---- config 1: R-pentomino known answers -------------------------------------------------
     rp = ref.parse("b2o$2o$bo!")
@@ -207,6 +273,9 @@ def main() -> None:
                         hash_in=np.concatenate([wsoups, np.zeros((1, 64), dtype=np.uint64), ~np.zeros((1, 64), dtype=np.uint64)]),
                         hash_out=np.array([ref.hash(x) for x in np.concatenate(
                             [wsoups, np.zeros((1, 64), dtype=np.uint64), ~np.zeros((1, 64), dtype=np.uint64)])], dtype=np.uint64))
+
+    # ---- 8f rank 4: Mirrored / Convolve / Match / InteractionOffsets / RLE -----------------------
+    make_locate(ref, port)
 
     for f in sorted(os.listdir(OUT)):
         if f.endswith(".npz"):

@@ -348,3 +348,98 @@ def test_port_vs_reference_next_rows(port, ref):
     assert (port.weld_step(w, 4) == ref.weld_step(w, 4)).all()
     assert (port.interaction_counts(s) == ref.interaction_counts(s)).all()
     assert all(port.hash(x) == ref.hash(x) for x in s)
+
+
+# ---- Mirrored / Convolve / Match / InteractionOffsets / RLE ------------------
+def test_port_locate_golden(port):
+    g = golden("locate.npz")
+    a, b = g["a"], g["b"]
+    for i in range(len(a)):
+        assert (port.mirrored(a[i]) == g["mirrored"][i]).all()
+        assert (port.convolve(a[i], b[i]) == g["convolve"][i]).all()
+        assert (port.convolve(b[i], a[i]) == g["convolve"][i]).all()  # the Minkowski sum commutes
+        assert (port.convolve(a[0], b[i]) == g["convolve_bcast"][i]).all()
+        assert (port.interaction_offsets(a[i], b[i]) == g["offsets"][i]).all()
+        assert (port.match_live_and_dead(a[i], b[i], port.mirrored(b[i])) == g["match_on_ab"][i]).all()
+    for i in range(len(g["states"])):
+        s, l, d = g["states"][i], g["live"][i], g["dead"][i]
+        assert (port.match_live(s, l) == g["match_live"][i]).all()
+        assert (port.match_live_and_dead(s, l, d) == g["match_live_and_dead"][i]).all()
+        assert (port.match_state(s, l) == g["match_state"][i]).all()
+        assert (port.match_target(s, g["targets"][i]) == g["match_target"][i]).all()
+        assert port.pop(g["match_state"][i]) >= 1  # the catalyst pasted into the soup is found
+    for s, text in zip(g["rle_in"], g["rle"]):
+        assert port.rle(s) == str(text)
+        assert (port.parse(str(text)) == port.moved(s, 32, 32)).all()  # RLE is written from cell (32, 32): a half-torus shift
+    for h, text in zip(g["history_in"], g["history_rle"]):
+        assert port.history_rle(h) == str(text)
+
+
+def test_port_match_is_the_definition(port):
+    """Match by brute force: offset (x, y) is ON iff every live cell lands on an ON cell and every dead cell
+    on an OFF cell (what MatchLiveAndDead's two convolutions compute, LifeAPI.hpp:432-435)."""
+    g = golden("locate.npz")
+    s, l, d = g["states"][1], g["live"][1], g["dead"][1]
+
+    def cells(p):
+        return [(x, y) for x in range(64) for y in range(64) if (int(p[x]) >> y) & 1]
+    lc, dc = cells(l), cells(d)
+    got = port.match_live_and_dead(s, l, d)
+    for x in range(0, 64, 5):
+        for y in range(64):
+            want = all((int(s[(x + i) & 63]) >> ((y + j) & 63)) & 1 for i, j in lc) and \
+                not any((int(s[(x + i) & 63]) >> ((y + j) & 63)) & 1 for i, j in dc)
+            assert bool((int(got[x]) >> y) & 1) == want
+
+
+def test_port_vs_reference_locate(port, ref):
+    rng = np.random.default_rng(4242)
+    for trial in range(24):
+        k = 1 + trial % 7
+        a = rng.integers(0, 1 << 63, size=(k, 64), dtype=np.uint64)
+        b = rng.integers(0, 1 << 63, size=(8 - k, 64), dtype=np.uint64)
+        a = np.bitwise_and.reduce(a, axis=0) << np.uint64(trial % 2)
+        b = np.bitwise_and.reduce(b, axis=0)
+        assert (port.mirrored(a) == ref.mirrored(a)).all()
+        assert (port.convolve(a, b) == ref.convolve(a, b)).all()
+        assert (port.interaction_offsets(a, b) == ref.interaction_offsets(a, b)).all()
+        assert (port.match_live(a, b) == ref.match_live(a, b)).all()
+        assert (port.match_state(a, b) == ref.match_state(a, b)).all()
+        assert (port.match_live_and_dead(a, b, port.mirrored(a)) == ref.match_live_and_dead(a, b, port.mirrored(a))).all()
+        assert port.rle(a) == ref.rle(a)
+        h = np.stack([a, b, a & b, port.mirrored(b)])
+        assert port.history_rle(h) == ref.history_rle(h)
+
+
+def test_library_rle_and_parse_golden(port):
+    """The product's host-side RLE writer / parser (lifeb200_rle ...; no GPU involved) against the reference's strings."""
+    from lifeapi_b200 import history_parse_rle, history_rle, parse_rle, rle
+    g = golden("locate.npz")
+    for s, text in zip(g["rle_in"], g["rle"]):
+        assert rle(s) == str(text)
+        assert (parse_rle(str(text)) == port.moved(s, 32, 32)).all()
+    for h, text in zip(g["history_in"], g["history_rle"]):
+        assert history_rle(h) == str(text)
+        back = history_parse_rle(str(text))  # 'F' cells (combinations StateToChar has no letter for) do not come back
+        assert not (back[0] & ~h[0]).any()  # every parsed state cell is a state cell of the record
+    assert rle(np.zeros(64, dtype=np.uint64)) == "!"
+    header = "x = 3, y = 3, rule = B3/S23\nbo$2bo$\n3o!\n"
+    assert (parse_rle(header) == port.parse(header)).all() and port.pop(parse_rle(header)) == 5
+    cat = golden("collisions.npz")
+    for c in cat["catalysts"]:
+        assert (parse_rle(rle(c)) == port.moved(c, 32, 32)).all()
+
+
+def test_library_rle_vs_reference_random(ref):
+    from lifeapi_b200 import history_parse_rle, history_rle, parse_rle, rle
+    rng = np.random.default_rng(99)
+    for trial in range(40):
+        planes = rng.integers(0, 1 << 63, size=(4, 1 + trial % 5, 64), dtype=np.uint64)
+        planes = np.bitwise_and.reduce(planes, axis=1) << np.uint64(trial % 2)
+        assert rle(planes[0]) == ref.rle(planes[0])
+        text = ref.history_rle(planes)
+        assert history_rle(planes) == text
+        assert (history_parse_rle(text) == ref.history_parse(text)).all()
+        assert (parse_rle(ref.rle(planes[1])) == ref.moved(planes[1], 32, 32)).all()
+    messy = "#C comment\r\nx = 3\r\n3o 2b o$$o!ignored"
+    assert (parse_rle(messy) == ref.parse(messy)).all()
