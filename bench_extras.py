@@ -133,7 +133,7 @@ def config5_survey(eng, p_int):
     cells = n * 4096.0 * gens
     return {"workload": f"config5 (1/16 scale): {n} on-device soups x {gens} gens, active iff state(G) != state(G-2)", "s": dt,
             "value": cells / dt / 1e9, "unit": "Gcell/s", "active": int(len(hits)), "pop_sum": int(pop_sum),
-            "hash_xor": f"{int(hash_xor):016x}", "int_pipe_frac_executed": cells * (10.0 / 32.0) / dt / p_int,
+            "hash_xor": f"{int(hash_xor):016x}", "int_pipe_frac_executed": cells * (9.5 / 32.0) / dt / p_int,
             "timing": "wall clock around the host-facing call, hits downloaded and sorted"}
 
 
@@ -177,6 +177,77 @@ def stable_propagate(eng, p_int):
             eng.free(p)
 
 
+def locate_rows(eng, p_int):
+    """SURVEY 8f rank 4 -- the steps either side of the stepping path, resident batches:
+    Match(LifeTarget) of one catalyst in 256 Ki evolved soups, and InteractionOffsets of one catalyst
+    against 256 Ki glider-sized objects (a soup masked to an 8x8 box)."""
+    n = 1 << 18
+    d_s, d_o, d_t = eng.malloc(n * 512), eng.malloc(n * 512), eng.malloc(1024)
+    try:
+        eng.soup_dev(d_s, 0, n, SEED, 0)
+        eng.step_batch_dev(d_s, d_s, n, 256)  # evolved soups: the ash a search would look through
+        eater = _pattern(STILL_LIFES["eater1"], 0, 0)
+        zoi = np.zeros(64, dtype=np.uint64)
+        for dx in (-1, 0, 1):
+            for dy in (-1, 0, 1):
+                zoi |= _pattern(STILL_LIFES["eater1"], dx, dy)
+        target = np.concatenate([eater, zoi & ~eater])  # LifeTarget(eater): wanted, unwanted = boundary
+        eng.h2d(d_t, target)
+        eng.sync()
+        ms = _time(eng, lambda: eng.match_target_batch_dev(d_s, n, d_t, 1, d_o))
+        found = np.empty((n, 64), dtype=np.uint64)
+        eng.d2h(found, d_o)
+        eng.sync()
+        out = {"match_target": {"workload": f"Match(LifeTarget(eater1)) over {n} soups evolved 256 gens", "ms": ms,
+                                "states_per_s": n / (ms * 1e-3), "hbm_gbs": 2 * n * 512 / (ms * 1e-3) / 1e9,
+                                "soups_with_an_eater": int((found != 0).any(axis=1).sum())}}
+        ref = _cpu_ref()
+        host = None
+        if ref is not None:
+            m = 1 << 12
+            host = np.empty((n, 64), dtype=np.uint64)
+            eng.d2h(host, d_s)
+            eng.sync()
+            t0 = time.perf_counter()
+            want = ref.match_target_batch(host[:m], target, 0)
+            dt = time.perf_counter() - t0
+            out["match_target"]["cpu_baseline"] = {"states_per_s": m / dt, "cores": ref.threads(), "kind": "reference",
+                                                   "sample": f"{m} states, {dt:.2f} s", "equal_on_sample": bool((want == found[:m]).all())}
+        # InteractionOffsets: catalyst (broadcast) x small objects
+        eng.soup_dev(d_s, 1 << 24, n, SEED, 0)
+        objs = np.empty((n, 64), dtype=np.uint64)
+        eng.d2h(objs, d_s)
+        eng.sync()
+        box = np.zeros(64, dtype=np.uint64)
+        box[:8] = np.uint64(0xFF)
+        objs &= box
+        eng.h2d(d_s, objs)
+        d_c = eng.malloc(512)
+        try:
+            eng.h2d(d_c, eater)
+            eng.sync()
+            ms = _time(eng, lambda: eng.interaction_offsets_dev(d_c, 1, d_s, n, d_o, n))
+            out["interaction_offsets"] = {"workload": f"eater1.InteractionOffsets(object) over {n} 8x8 objects", "ms": ms,
+                                          "pairs_per_s": n / (ms * 1e-3), "hbm_gbs": 2 * n * 512 / (ms * 1e-3) / 1e9}
+            if ref is not None:
+                m = 1 << 12
+                got = np.empty((n, 64), dtype=np.uint64)
+                eng.d2h(got, d_o)
+                eng.sync()
+                t0 = time.perf_counter()
+                want = ref.interaction_offsets_batch(eater, objs[:m], 0)
+                dt = time.perf_counter() - t0
+                out["interaction_offsets"]["cpu_baseline"] = {"pairs_per_s": m / dt, "cores": ref.threads(), "kind": "reference",
+                                                              "sample": f"{m} pairs, {dt:.2f} s",
+                                                              "equal_on_sample": bool((want == got[:m]).all())}
+        finally:
+            eng.free(d_c)
+        return out
+    finally:
+        for p in (d_s, d_o, d_t):
+            eng.free(p)
+
+
 def _d2d(eng, dst, src, nbytes):
     # device-to-device copy through the step entry point's gens == 0 path (a plain cudaMemcpyAsync D2D)
     return eng.lib.lifeb200_step_batch_dev(eng._h, src, dst, nbytes // 512, 0)
@@ -185,7 +256,7 @@ def _d2d(eng, dst, src, nbytes):
 def run_extras(eng, p_int):
     out = {}
     for name, fn in (("config3", config3_unknown_step), ("config4", config4_enumeration), ("config5", config5_survey),
-                     ("stable_propagate", stable_propagate)):
+                     ("stable_propagate", stable_propagate), ("locate", locate_rows)):
         try:
             out[name] = fn(eng, p_int)
         except Exception as e:  # noqa: BLE001  (a side measurement must not kill the headline)

@@ -8,7 +8,7 @@
 // are exchanged with __shfl_sync whose width=LPP argument gives the torus wrap.
 //
 // The rule is LifeState::StepAlt (LifeAPI.hpp:1218-1254) restated as 3-input LUTs:
-//   per 32-cell half-word and generation: 2 SHF + 8 LOP3 (SURVEY.md 8d counts 2 + 10 for the literal form).
+//   per 32-cell half-word and generation: 2 SHF + 7.5 LOP3 (SURVEY.md 8d counts 2 + 10 for the literal form).
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -68,28 +68,31 @@ __device__ __forceinline__ uint32_t rule32(uint32_t a, uint32_t u0, uint32_t u1,
   return lop3<0x09>(g2, ya, xa);
 }
 
-// Pair-shared form of the same select, found by SAT-based exact synthesis (tools/lut_synth_pair_z3.py,
-// solution in tools/pair_0_4_4.solution.txt) and checked on all inputs in tests/test_oracle.py:
-// four LUTs turn the 2-bit counts (a, b) of two adjacent columns into a 3-signal code of a+b that is
-// shared by BOTH columns of the pair; four more give next = [a+b+c == 3] | cell & [a+b+c == 4] from
-// that code, the count c of the column on the far side and the centre cell.  8 + 4 = 12 LOP3 per two
-// half-words instead of 2 x 7.
+// Pair-shared form of the same select, found by SAT-based exact synthesis (tools/lut_synth_pair_cnf.py,
+// `0 3 4 --dc --raw`; every smaller split of the same family is UNSAT) and checked on all
+// inputs in tests/test_oracle.py: three LUTs turn the 2-bit counts (a, b) of two adjacent columns into
+// a 3-signal code of a+b that is shared by BOTH columns of the pair; four more per column give
+// next = [a+b+c == 3] | cell & [a+b+c == 4] from that code, the count c of the column on the far side,
+// the low count bits of the pair and the centre cell.  3 + 2 x 4 = 11 LOP3 per two half-words.
+// The select uses the don't-cares of the count: the cell is the middle bit of its own column's
+// triple, so cell = 1 implies count >= 1 and count = 3 implies cell = 1; it is exact on every
+// (a, b, c, cell) a real column can produce, for the left and for the right column of the pair alike.
 struct PairCode {
-  uint32_t p8, p9, p10;
+  uint32_t p0, p1, p2;
 };
 __device__ __forceinline__ PairCode pair_code(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1) {
   PairCode p;
-  const uint32_t g7 = lop3<0xB2>(a1, b0, b1);
-  p.p8 = lop3<0x17>(a1, b0, b1);
-  p.p9 = lop3<0xBC>(a0, b0, g7);
-  p.p10 = lop3<0x23>(b0, g7, p.p9);
+  p.p0 = lop3<0xB2>(a1, b0, b1);
+  p.p1 = lop3<0xD4>(a1, b1, p.p0);
+  p.p2 = lop3<kMaj>(a0, b0, p.p0);
   return p;
 }
-__device__ __forceinline__ uint32_t pair_select(const PairCode& p, uint32_t c0, uint32_t c1, uint32_t cell) {
-  const uint32_t g11 = lop3<0xDA>(c0, cell, p.p9);
-  const uint32_t g12 = lop3<0x98>(cell, p.p10, g11);
-  const uint32_t g13 = lop3<0xF1>(c1, g11, g12);
-  return lop3<0x94>(p.p8, g12, g13);
+__device__ __forceinline__ uint32_t pair_select(const PairCode& p, uint32_t a0, uint32_t b0, uint32_t c0, uint32_t c1,
+                                                uint32_t cell) {
+  const uint32_t t0 = lop3<kMaj>(c0, p.p0, p.p2);
+  const uint32_t t1 = lop3<0x16>(c1, p.p1, t0);
+  const uint32_t t2 = lop3<kXor3>(c0, a0, b0);  // bit 0 of the 3x3 sum
+  return lop3<0xC8>(cell, t1, t2);
 }
 
 template <int LPP>
@@ -130,7 +133,7 @@ struct Tile {
 
   // One generation in place == LifeState::Step() (LifeAPI.hpp:1196-1216).  Words are taken two at a
   // time: the pair code of (cnt[w], cnt[w+1]) is shared by both words, so a generation costs, per
-  // 32-cell half-word, 2 SHF + 2 LOP3 (column count) + 2 (half a pair code) + 4 (select) = 10
+  // 32-cell half-word, 2 SHF + 2 LOP3 (column count) + 1.5 (half a pair code) + 4 (select) = 9.5
   // integer-pipe instructions.  Updating in place is safe because every neighbour enters through
   // column counts taken before the word is overwritten.
   __device__ __forceinline__ void step(int sub) {
@@ -147,10 +150,10 @@ struct Tile {
       const Cnt c2 = (w + 2 == W) ? after : (w + 2 == W - 1) ? last : count_rows(lo[w + 2], hi[w + 2]);
       const PairCode plo = pair_code(c0.b0lo, c0.b1lo, c1.b0lo, c1.b1lo);
       const PairCode phi = pair_code(c0.b0hi, c0.b1hi, c1.b0hi, c1.b1hi);
-      lo[w] = pair_select(plo, prev.b0lo, prev.b1lo, lo[w]);
-      hi[w] = pair_select(phi, prev.b0hi, prev.b1hi, hi[w]);
-      lo[w + 1] = pair_select(plo, c2.b0lo, c2.b1lo, lo[w + 1]);
-      hi[w + 1] = pair_select(phi, c2.b0hi, c2.b1hi, hi[w + 1]);
+      lo[w] = pair_select(plo, c0.b0lo, c1.b0lo, prev.b0lo, prev.b1lo, lo[w]);
+      hi[w] = pair_select(phi, c0.b0hi, c1.b0hi, prev.b0hi, prev.b1hi, hi[w]);
+      lo[w + 1] = pair_select(plo, c0.b0lo, c1.b0lo, c2.b0lo, c2.b1lo, lo[w + 1]);
+      hi[w + 1] = pair_select(phi, c0.b0hi, c1.b0hi, c2.b0hi, c2.b1hi, hi[w + 1]);
       prev = c1;
       c0 = c2;
     }

@@ -303,27 +303,36 @@ def test_port_unknown_step_sop_vs_reference_and_semantics(port, ref):
 
 
 def test_pair_shared_rule_luts_exhaustive():
-    """pair_code / pair_select in csrc/life_core.cuh: the code of (a, b) serves both columns of a pair."""
+    """pair_code / pair_select in csrc/life_core.cuh: the code of (a, b) serves both columns of a pair.  The
+    select relies on the count's don't-cares (the cell is the middle bit of its own column's triple: cell = 1
+    implies count >= 1, count = 3 implies cell = 1), so it is checked on every input a column can produce,
+    once with the cell belonging to column a (left use) and once to column b (right use)."""
     import os
     import re
     from conftest import ROOT
     src = open(os.path.join(ROOT, "lifeapi_b200", "csrc", "life_core.cuh")).read()
     body = src[src.index("PairCode pair_code("):src.index("template <int LPP>\n__device__ __forceinline__ Cnt halo")]
-    assert [int(m, 16) for m in re.findall(r"lop3<(0x\w+)>", body)] == [0xB2, 0x17, 0xBC, 0x23, 0xDA, 0x98, 0xF1, 0x94]
+    body = body.replace("kMaj", "0xE8").replace("kXor3", "0x96")
+    assert [int(m, 16) for m in re.findall(r"lop3<(0x\w+)>", body)] == [0xB2, 0xD4, 0xE8, 0xE8, 0x16, 0x96, 0xC8]
+    checked = 0
     for ca in range(4):
         for cb in range(4):
             a0, a1, b0, b1 = ca & 1, ca >> 1, cb & 1, cb >> 1
-            g7 = _lop3(0xB2, a1, b0, b1)
-            p8 = _lop3(0x17, a1, b0, b1)
-            p9 = _lop3(0xBC, a0, b0, g7)
-            p10 = _lop3(0x23, b0, g7, p9)
+            p0 = _lop3(0xB2, a1, b0, b1)
+            p1 = _lop3(0xD4, a1, b1, p0)
+            p2 = _lop3(0xE8, a0, b0, p0)
             for co in range(4):
                 for cell in (0, 1):
-                    g11 = _lop3(0xDA, co & 1, cell, p9)
-                    g12 = _lop3(0x98, cell, p10, g11)
-                    g13 = _lop3(0xF1, co >> 1, g11, g12)
-                    n = ca + cb + co
-                    assert _lop3(0x94, p8, g12, g13) == int(n == 3 or (cell and n == 4))
+                    for own in (ca, cb):
+                        if (cell == 1 and own == 0) or (cell == 0 and own == 3):
+                            continue  # no column has a live centre and an empty triple, or a full triple and a dead centre
+                        t0 = _lop3(0xE8, co & 1, p0, p2)
+                        t1 = _lop3(0x16, co >> 1, p1, t0)
+                        t2 = _lop3(0x96, co & 1, a0, b0)
+                        n = ca + cb + co
+                        assert _lop3(0xC8, cell, t1, t2) == int(n == 3 or (cell and n == 4))
+                        checked += 1
+    assert checked == 192
 
 
 # ---- 8f next rows ---------------------------------------------------------------------------------

@@ -8,6 +8,7 @@ per column finish  next = [T_x + T_x+1 + T_far == 3] | cell & [.. == 4].  Cost p
 = GP + 2*GT LOP3 (today: 4 + 2*4).
 
 --raw tail gates may also read the pair's four raw count bits, not only the code gates.
+--gtr N  (with --dc) the right column's tail has N gates instead of GT.
 --dc  synthesise the left and the right column's tail separately (same gate count, their own
       LUT constants and wiring) and use the don't-cares each has: the cell is the middle bit of
       its own column's triple, so cell=1 implies T_own >= 1 and T_own = 3 implies cell = 1.
@@ -50,7 +51,7 @@ class Cnf:
             f.write(" ".join(map(str, c)) + " 0\n")
 
 
-def build(code, GP, GT, dc, raw=False):
+def build(code, GP, GT, dc, raw=False, GTR=None):
     enc = CODES[code]
     cnf = Cnf()
     pair_rows = list(itertools.product(range(4), range(4)))            # (ca, cb)
@@ -111,7 +112,7 @@ def build(code, GP, GT, dc, raw=False):
         code_sigs.append((f"p{g}", s))
     code_gate_sigs = code_sigs[4:]
 
-    def synth_tail(tag, rows, own):
+    def synth_tail(tag, rows, own, GT=GT):
         """own = 0: the cell belongs to column a (left), 1: to column b (right), None: no don't-cares."""
         idx_pair = [pair_rows.index((ca, cb)) for ca, cb, co, cell in rows]
 
@@ -147,7 +148,7 @@ def build(code, GP, GT, dc, raw=False):
 
     if dc:
         synth_tail("l", cares(0), 0)
-        synth_tail("r", cares(1), 1)
+        synth_tail("r", cares(1), 1, GTR if GTR is not None else GT)
     else:
         synth_tail("t", tail_rows, None)
 
@@ -194,18 +195,19 @@ def solve(cnf, timeout):
 
 
 def main():
-    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    args = [a for i, a in enumerate(sys.argv[1:], 1) if not a.startswith("--") and sys.argv[i - 1] not in ("--timeout", "--gtr")]
     code, GP, GT = map(int, args[:3])
     dc = "--dc" in sys.argv
     timeout = None
     if "--timeout" in sys.argv:
         timeout = float(sys.argv[sys.argv.index("--timeout") + 1])
     raw = "--raw" in sys.argv
-    cnf, gates = build(code, GP, GT, dc, raw)
+    gtr = int(sys.argv[sys.argv.index("--gtr") + 1]) if "--gtr" in sys.argv else None
+    cnf, gates = build(code, GP, GT, dc, raw, gtr)
     t0 = time.time()
     status, model = solve(cnf, timeout)
     dt = time.time() - t0
-    print(f"code {code} GP {GP} GT {GT} dc {dc} raw {raw}: vars {cnf.n} clauses {len(cnf.clauses)} -> {status} in {dt:.1f}s", flush=True)
+    print(f"code {code} GP {GP} GT {GT} GTR {gtr} dc {dc} raw {raw}: vars {cnf.n} clauses {len(cnf.clauses)} -> {status} in {dt:.1f}s", flush=True)
     if model:
         for name, cands, sel, lut in gates:
             ins = [cands[[model.get(v, False) for v in sel[k]].index(True)] for k in range(3)]
