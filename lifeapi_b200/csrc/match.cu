@@ -60,7 +60,7 @@ __device__ __forceinline__ void run_match(Tile<LPP>& t, const Tile<LPP>& wm, con
 }
 
 template <int LPP>
-__global__ void __launch_bounds__(kBlockM) step_match_kernel(const uint64_t* __restrict__ patterns,
+__global__ void __launch_bounds__(kBlockM, 1) step_match_kernel(const uint64_t* __restrict__ patterns,
                                                              const uint64_t* __restrict__ targets,
                                                              const uint32_t* __restrict__ target_index, size_t n,
                                                              uint64_t first_id, unsigned gens, unsigned stable_interval,
@@ -97,7 +97,7 @@ __device__ __forceinline__ uint64_t rotl64v(uint64_t v, unsigned s) {
 
 // tables: [cat | catZOI | proj | projZOI], each entry 64 words.
 template <int LPP>
-__global__ void __launch_bounds__(kBlockM) enumerate_kernel(const uint64_t* __restrict__ cat,
+__global__ void __launch_bounds__(kBlockM, 1) enumerate_kernel(const uint64_t* __restrict__ cat,
                                                             const uint64_t* __restrict__ cat_zoi,
                                                             const uint64_t* __restrict__ proj,
                                                             const uint64_t* __restrict__ proj_zoi, unsigned n_proj,
@@ -181,7 +181,7 @@ __device__ __forceinline__ void block_accumulate(uint64_t pop, uint64_t h, unsig
 }
 
 template <int LPP>
-__global__ void __launch_bounds__(kBlockM) survey_kernel(uint64_t first_id, size_t n, uint64_t seed, int dist,
+__global__ void __launch_bounds__(kBlockM, 1) survey_kernel(uint64_t first_id, size_t n, uint64_t seed, int dist,
                                                          unsigned gens, lifeb200_hit* hits, size_t cap,
                                                          unsigned long long* n_hits, unsigned long long* pop_sum,
                                                          unsigned long long* hash_xor) {

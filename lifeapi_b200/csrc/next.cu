@@ -15,7 +15,7 @@ static inline unsigned grid_n(size_t n, int lpp) { return (unsigned)((n * (size_
 
 // ---- LifeWeld::Step: 3x3 count (bit3 dropped, as the reference does) + frozen count, then the rule ----
 template <int LPP>
-__global__ void __launch_bounds__(kBlockN) weld_step_kernel(uint64_t* __restrict__ records, size_t n, unsigned gens) {
+__global__ void __launch_bounds__(kBlockN, 1) weld_step_kernel(uint64_t* __restrict__ records, size_t n, unsigned gens) {
   constexpr int W = Tile<LPP>::W;
   const size_t p = ((size_t)blockIdx.x * kBlockN + threadIdx.x) / LPP;
   const int sub = threadIdx.x & (LPP - 1);

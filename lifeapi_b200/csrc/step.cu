@@ -8,13 +8,18 @@
 namespace lifeb200 {
 
 constexpr int kBlock = 256;
+// The step kernel is bound by the integer pipe, not by occupancy: with the register budget of one
+// small CTA per SM (min blocks = 1) ptxas keeps every column count of a generation in flight instead of
+// squeezing to 64 registers, and the ALU pipe goes from 95-96% to 99% busy (tools/ubench_step.cu,
+// profiles/r01h_ubench_step.txt).
+constexpr int kStepBlock = 128;
 
 // Each warp owns 32/LPP whole patterns; `gens` generations run in registers between one
 // 128-bit vectorised load and one 128-bit vectorised store per 16 bytes of state.
 template <int LPP>
-__global__ void __launch_bounds__(kBlock) step_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
-                                                      size_t n, unsigned gens) {
-  const size_t gid = (size_t)blockIdx.x * kBlock + threadIdx.x;
+__global__ void __launch_bounds__(kStepBlock, 1) step_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
+                                                              size_t n, unsigned gens) {
+  const size_t gid = (size_t)blockIdx.x * kStepBlock + threadIdx.x;
   const size_t p = gid / LPP;
   const int sub = threadIdx.x & (LPP - 1);
   const bool valid = p < n;
@@ -98,11 +103,11 @@ static inline unsigned grid_for(size_t n, int lpp) {
 
 int launch_step(lifeb200_ctx* ctx, cudaStream_t st, const uint64_t* in, uint64_t* out, size_t n, unsigned gens) {
   if (n == 0) return LIFEB200_OK;
-  // Measured on B200 (profiles/r01_*): 4 lanes per pattern (16 words per lane) keeps the ALU pipe
-  // busiest when many generations run per launch; with few generations the launch is HBM-bound and
+  // Measured on B200 (profiles/r01h_ubench_step.txt): 8 lanes per pattern (8 words per lane) keeps the ALU
+  // pipe busiest when many generations run per launch; with few generations the launch is HBM-bound and
   // 16 lanes per pattern (32 contiguous bytes per lane) coalesces best.
-  int lpp = ctx->lpp ? ctx->lpp : (gens >= 8 ? 4 : 16);
-  LIFEB200_DISPATCH_LPP(lpp, (step_kernel<LPP><<<grid_for(n, LPP), kBlock, 0, st>>>(in, out, n, gens)));
+  int lpp = ctx->lpp ? ctx->lpp : (gens >= 8 ? 8 : 16);
+  LIFEB200_DISPATCH_LPP(lpp, (step_kernel<LPP><<<(unsigned)((n * (size_t)LPP + kStepBlock - 1) / kStepBlock), kStepBlock, 0, st>>>(in, out, n, gens)));
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }

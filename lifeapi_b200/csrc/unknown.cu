@@ -34,7 +34,7 @@ __device__ __forceinline__ void unknown_step_tile(Tile<LPP>& s, Tile<LPP>& u, in
 }
 
 template <int LPP>
-__global__ void __launch_bounds__(kBlockU) unknown_step_kernel(const uint64_t* __restrict__ state_in,
+__global__ void __launch_bounds__(kBlockU, 1) unknown_step_kernel(const uint64_t* __restrict__ state_in,
                                                                const uint64_t* __restrict__ unknown_in,
                                                                uint64_t* __restrict__ state_out,
                                                                uint64_t* __restrict__ unknown_out, size_t n,
@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(kBlockU) unknown_step_kernel(const uint64_t* _
 // has no stepping member for it; the build-defined step is state.Step(); history |= state
 // (LifeAPI.hpp:1196-1216 and :255-260), repeated `gens` times.  marked / original are untouched.
 template <int LPP>
-__global__ void __launch_bounds__(kBlockU) history_step_kernel(uint64_t* __restrict__ records, size_t n, unsigned gens) {
+__global__ void __launch_bounds__(kBlockU, 1) history_step_kernel(uint64_t* __restrict__ records, size_t n, unsigned gens) {
   const size_t gid = (size_t)blockIdx.x * kBlockU + threadIdx.x;
   const size_t p = gid / LPP;
   const int sub = threadIdx.x & (LPP - 1);
