@@ -32,7 +32,7 @@ SEED = 0x4C696665415049
 N_SOUPS = 1 << 20
 GENS = 1024
 INSTR_PER_CELL = 12.0 / 32.0  # algorithmic 2 SHF + 10 LOP3 per 32 cells per generation
-EXECUTED_INSTR_PER_CELL = 9.5 / 32.0  # what step_kernel issues (pair-shared select with don't-cares)
+EXECUTED_INSTR_PER_CELL = 8.5 / 32.0  # what step_kernel issues: row-interleaved layout + pair-shared select
 # dram bytes of one 1 Mi-soup x 1024-generation step_kernel launch from the committed ncu capture
 # (profiles/r01d_step_kernel_lpp4_raw.csv: dram__bytes_read.sum 546.79 MB + dram__bytes_write.sum 488.76 MB;
 # the write side is below 512 MiB because the tail of the output is still in the 126 MB L2 at kernel end)
@@ -339,7 +339,7 @@ def main():
                 "algorithmic_bytes": 2 * nbytes,
                 "kernel": "step_kernel<LPP>", "kernel_ms": kernel_ms,
                 "algorithmic": "12 int-pipe instr per 32 cells per generation = 0.375 instr/cell-update (SURVEY 8d)",
-                "executed": "9.5 int-pipe instr per 32 cells per generation (2 SHF + 7.5 LOP3, pair-shared select)",
+                "executed": "8.5 int-pipe instr per 32 cells per generation (1 SHF + 7.5 LOP3: row-interleaved registers, pair-shared select)",
                 "pipe_utilisation": per_gpu_cells_s * EXECUTED_INSTR_PER_CELL / p_int,
                 "peak_source": f"LOP3 microbenchmark in this run (lifeb200_measure_int_peak): {p_int / 1e12:.2f} T/s = "
                                f"{info['sm_count']} SMs x 64 lanes x {mhz_eff:.0f} MHz effective",

@@ -50,6 +50,56 @@ __device__ __forceinline__ Cnt count_rows(uint32_t lo, uint32_t hi) {
   return c;
 }
 
+// ---- row-interleaved register layout ("IL") -----------------------------------------------------
+// In the reference layout the low register of a column holds rows 0..31 and the high one rows
+// 32..63, so both row neighbours of a cell sit in the SAME register one bit away: two funnel
+// shifts per register and generation.  Interleaved, the low register holds the EVEN rows (bit k =
+// row 2k) and the high one the ODD rows (bit k = row 2k+1).  Then the row below an even row is the
+// same bit of the odd register and the row above it the odd register rotated by one; for an odd
+// row it is the even register as is, and the even register rotated the other way.  One 32-bit
+// rotate per register and generation instead of two; the torus wrap 63 -> 0 is the rotate's own
+// wrap.  Everything after the column count is bit-position-wise and does not change.  Kernels that
+// run many generations convert once after the load and once before the store (about 35 integer
+// instructions per word each way, against 17 per word and generation).
+__device__ __forceinline__ Cnt count_rows_il(uint32_t ev, uint32_t od) {
+  const uint32_t up = __funnelshift_l(od, od, 1);  // row 2k-1 at bit k
+  const uint32_t dn = __funnelshift_r(ev, ev, 1);  // row 2k+2 at bit k
+  Cnt c;
+  c.b0lo = lop3<kXor3>(up, ev, od);
+  c.b1lo = lop3<kMaj>(up, ev, od);
+  c.b0hi = lop3<kXor3>(ev, od, dn);
+  c.b1hi = lop3<kMaj>(ev, od, dn);
+  return c;
+}
+// even bits of x to the low half, odd bits to the high half (outer perfect unshuffle) and back
+__device__ __forceinline__ uint32_t unshuffle32(uint32_t x) {
+  uint32_t t;
+  t = (x ^ (x >> 1)) & 0x22222222u; x ^= t ^ (t << 1);
+  t = (x ^ (x >> 2)) & 0x0C0C0C0Cu; x ^= t ^ (t << 2);
+  t = (x ^ (x >> 4)) & 0x00F000F0u; x ^= t ^ (t << 4);
+  t = (x ^ (x >> 8)) & 0x0000FF00u; x ^= t ^ (t << 8);
+  return x;
+}
+__device__ __forceinline__ uint32_t shuffle32(uint32_t x) {
+  uint32_t t;
+  t = (x ^ (x >> 8)) & 0x0000FF00u; x ^= t ^ (t << 8);
+  t = (x ^ (x >> 4)) & 0x00F000F0u; x ^= t ^ (t << 4);
+  t = (x ^ (x >> 2)) & 0x0C0C0C0Cu; x ^= t ^ (t << 2);
+  t = (x ^ (x >> 1)) & 0x22222222u; x ^= t ^ (t << 1);
+  return x;
+}
+// (rows 0..31, rows 32..63) -> (even rows, odd rows) of one column word, and back
+__device__ __forceinline__ void to_interleaved(uint32_t& lo, uint32_t& hi) {
+  const uint32_t a = unshuffle32(lo), b = unshuffle32(hi);
+  lo = __byte_perm(a, b, 0x5410);  // even rows of 0..31 below even rows of 32..63
+  hi = __byte_perm(a, b, 0x7632);  // odd rows likewise
+}
+__device__ __forceinline__ void from_interleaved(uint32_t& lo, uint32_t& hi) {
+  const uint32_t a = __byte_perm(lo, hi, 0x5410), b = __byte_perm(lo, hi, 0x7632);
+  lo = shuffle32(a);
+  hi = shuffle32(b);
+}
+
 // B3/S23 select over the three column counts (the job of the StepAlt tail, LifeAPI.hpp:1236-1252).
 // X = u0+c0+d0 and Y = u1+c1+d1 are each encoded in two LUTs -- X as (not-all-equal, majority),
 // a Gray code of 0..3, Y as (parity, majority) -- and next = [X+2Y == 3] | a & [X+2Y == 4] is then
@@ -133,21 +183,24 @@ struct Tile {
 
   // One generation in place == LifeState::Step() (LifeAPI.hpp:1196-1216).  Words are taken two at a
   // time: the pair code of (cnt[w], cnt[w+1]) is shared by both words, so a generation costs, per
-  // 32-cell half-word, 2 SHF + 2 LOP3 (column count) + 1.5 (half a pair code) + 4 (select) = 9.5
-  // integer-pipe instructions.  Updating in place is safe because every neighbour enters through
-  // column counts taken before the word is overwritten.
+  // 32-cell register, 2 LOP3 (column count) + 1.5 (half a pair code) + 4 (select) = 7.5 LOP3 plus the
+  // row shifts: 2 SHF in the reference layout (9.5 integer-pipe instructions), 1 SHF when the tile is
+  // row-interleaved (IL = true: 8.5).  Updating in place is safe because every neighbour enters
+  // through column counts taken before the word is overwritten.
+  template <bool IL = false>
   __device__ __forceinline__ void step(int sub) {
     static_assert(W % 2 == 0, "words are processed in pairs");
     const int up_src = sub + LPP - 1, dn_src = sub + 1;  // taken modulo LPP by shfl width
-    Cnt first = count_rows(lo[0], hi[0]);
-    Cnt last = count_rows(lo[W - 1], hi[W - 1]);
+    auto rows = [](uint32_t l, uint32_t h) { return IL ? count_rows_il(l, h) : count_rows(l, h); };
+    Cnt first = rows(lo[0], hi[0]);
+    Cnt last = rows(lo[W - 1], hi[W - 1]);
     Cnt prev = halo<LPP>(last, up_src);
     Cnt after = halo<LPP>(first, dn_src);
     Cnt c0 = first;
 #pragma unroll
     for (int w = 0; w < W; w += 2) {
-      const Cnt c1 = (w + 1 == W - 1) ? last : count_rows(lo[w + 1], hi[w + 1]);
-      const Cnt c2 = (w + 2 == W) ? after : (w + 2 == W - 1) ? last : count_rows(lo[w + 2], hi[w + 2]);
+      const Cnt c1 = (w + 1 == W - 1) ? last : rows(lo[w + 1], hi[w + 1]);
+      const Cnt c2 = (w + 2 == W) ? after : (w + 2 == W - 1) ? last : rows(lo[w + 2], hi[w + 2]);
       const PairCode plo = pair_code(c0.b0lo, c0.b1lo, c1.b0lo, c1.b1lo);
       const PairCode phi = pair_code(c0.b0hi, c0.b1hi, c1.b0hi, c1.b1hi);
       lo[w] = pair_select(plo, c0.b0lo, c1.b0lo, prev.b0lo, prev.b1lo, lo[w]);
@@ -157,6 +210,15 @@ struct Tile {
       prev = c1;
       c0 = c2;
     }
+  }
+  // reference layout <-> row-interleaved layout of every word of the tile (see count_rows_il)
+  __device__ __forceinline__ void interleave() {
+#pragma unroll
+    for (int w = 0; w < W; w++) to_interleaved(lo[w], hi[w]);
+  }
+  __device__ __forceinline__ void deinterleave() {
+#pragma unroll
+    for (int w = 0; w < W; w++) from_interleaved(lo[w], hi[w]);
   }
 
   // NeighbourCount(const LifeState&) (NeighbourCount.hpp:40-70 == LifeAPI.hpp:909-952): the four

@@ -13,6 +13,9 @@ constexpr int kBlock = 256;
 // squeezing to 64 registers, and the ALU pipe goes from 95-96% to 99% busy (tools/ubench_step.cu,
 // profiles/r01h_ubench_step.txt).
 constexpr int kStepBlock = 128;
+// From this many generations per launch the tile is stepped in the row-interleaved layout (one shift
+// per register and generation instead of two, life_core.cuh); the conversions cost about 4 generations.
+constexpr unsigned kInterleaveFrom = 16;
 
 // Each warp owns 32/LPP whole patterns; `gens` generations run in registers between one
 // 128-bit vectorised load and one 128-bit vectorised store per 16 bytes of state.
@@ -30,8 +33,15 @@ __global__ void __launch_bounds__(kStepBlock, 1) step_kernel(const uint64_t* __r
 #pragma unroll
     for (int w = 0; w < Tile<LPP>::W; w++) t.lo[w] = t.hi[w] = 0;
   }
+  if (gens >= kInterleaveFrom) {  // warp-uniform: many generations pay for the two layout conversions
+    t.interleave();
 #pragma unroll 1
-  for (unsigned g = 0; g < gens; g++) t.step(sub);
+    for (unsigned g = 0; g < gens; g++) t.template step<true>(sub);
+    t.deinterleave();
+  } else {
+#pragma unroll 1
+    for (unsigned g = 0; g < gens; g++) t.template step<false>(sub);
+  }
   if (valid) t.store(out + p * kN, sub);
 }
 
