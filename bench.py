@@ -32,7 +32,7 @@ SEED = 0x4C696665415049
 N_SOUPS = 1 << 20
 GENS = 1024
 INSTR_PER_CELL = 12.0 / 32.0  # algorithmic 2 SHF + 10 LOP3 per 32 cells per generation
-EXECUTED_INSTR_PER_CELL = 8.5 / 32.0  # what step_kernel issues: row-interleaved layout + pair-shared select
+EXECUTED_INSTR_PER_CELL = 7.75 / 32.0  # what step_kernel_x<8> issues: 4 patterns bit-interleaved per register + pair-shared select
 # dram bytes of one 1 Mi-soup x 1024-generation step_kernel launch from the committed ncu capture
 # (profiles/r01d_step_kernel_lpp4_raw.csv: dram__bytes_read.sum 546.79 MB + dram__bytes_write.sum 488.76 MB;
 # the write side is below 512 MiB because the tail of the output is still in the 126 MB L2 at kernel end)
@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--soups", type=int, default=N_SOUPS, help="soups per GPU (default: BASELINE config 2)")
     ap.add_argument("--gens", type=int, default=GENS)
     ap.add_argument("--lpp", type=int, default=0, help="lanes per pattern override (tuning)")
+    ap.add_argument("--layout", type=int, default=0, help="step-kernel register layout override 1/2/4/8 (tuning)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the config 3/4/5 side measurements")
@@ -226,6 +227,8 @@ def main():
     eng = Engine(local_rank)
     if args.lpp:
         eng.set_lanes_per_pattern(args.lpp)
+    if args.layout:
+        eng.set_step_layout(args.layout)
     info = eng.device_info()
     n, gens = args.soups, args.gens
     first_id = rank * n
@@ -337,9 +340,9 @@ def main():
                 "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of this launch shape "
                                   "(profiles/, see DESIGN.md 6); algorithmic = 2 x 512 B x soups",
                 "algorithmic_bytes": 2 * nbytes,
-                "kernel": "step_kernel<LPP>", "kernel_ms": kernel_ms,
+                "kernel": "step_kernel_x<8>", "kernel_ms": kernel_ms,
                 "algorithmic": "12 int-pipe instr per 32 cells per generation = 0.375 instr/cell-update (SURVEY 8d)",
-                "executed": "8.5 int-pipe instr per 32 cells per generation (1 SHF + 7.5 LOP3: row-interleaved registers, pair-shared select)",
+                "executed": "7.75 int-pipe instr per 32 cells per generation (0.25 SHF + 7.5 LOP3: rows by class mod 8, 4 patterns bit-interleaved per register, pair-shared select)",
                 "pipe_utilisation": per_gpu_cells_s * EXECUTED_INSTR_PER_CELL / p_int,
                 "peak_source": f"LOP3 microbenchmark in this run (lifeb200_measure_int_peak): {p_int / 1e12:.2f} T/s = "
                                f"{info['sm_count']} SMs x 64 lanes x {mhz_eff:.0f} MHz effective",
@@ -361,7 +364,7 @@ def main():
                 "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e,
                 "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "other_configs": extras, "survey_gather": survey_gather,
                 "checksum": {"pop_sum": int(pop_sum), "hash_xor": f"{int(hash_xor):016x}"},
-                "lanes_per_pattern": args.lpp or "default", "device": {"sms": info["sm_count"], "cc": list(info["cc"])}}
+                "lanes_per_pattern": args.lpp or "default", "step_layout": args.layout or "auto", "device": {"sms": info["sm_count"], "cc": list(info["cc"])}}
         print(json.dumps(line), flush=True)
 
     eng.free(d_in)

@@ -55,6 +55,11 @@ int lifeb200_device_info(lifeb200_ctx* ctx, int* sm_count, int* cc_major, int* c
 /* Choose the lane-group width of the step kernels: lanes per pattern in {1,2,4,8,16,32};
  * 0 restores the default.  Results never depend on it. */
 int lifeb200_set_lanes_per_pattern(lifeb200_ctx* ctx, int lpp);
+/* Choose the REGISTER layout lifeb200_step_batch_* steps in (HBM layout and results never change):
+ * 1 = the reference's, 2 = even/odd rows per register, 4 / 8 = rows by class mod 4 / 8 with 2 / 4
+ * patterns bit-interleaved per register (fewer shifts per generation, a conversion per launch);
+ * 0 restores the default (chosen from the generation count). */
+int lifeb200_set_step_layout(lifeb200_ctx* ctx, int layout);
 
 /* ---- memory ---------------------------------------------------------------------------- */
 int lifeb200_malloc(lifeb200_ctx* ctx, void** dptr, size_t bytes);

@@ -132,6 +132,14 @@ int lifeb200_device_info(lifeb200_ctx* ctx, int* sm_count, int* cc_major, int* c
   return LIFEB200_OK;
 }
 
+int lifeb200_set_step_layout(lifeb200_ctx* ctx, int layout) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (layout != 0 && layout != 1 && layout != 2 && layout != 4 && layout != 8)
+    return set_error(LIFEB200_E_ARG, "step layout must be 0 (auto), 1, 2, 4 or 8 (got %d)", layout);
+  ctx->step_layout = layout;
+  return LIFEB200_OK;
+}
+
 int lifeb200_set_lanes_per_pattern(lifeb200_ctx* ctx, int lpp) {
   if (!ctx) return set_error(LIFEB200_E_ARG, "null context");
   if (lpp != 0 && lpp != 1 && lpp != 2 && lpp != 4 && lpp != 8 && lpp != 16 && lpp != 32)

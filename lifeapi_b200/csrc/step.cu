@@ -4,6 +4,7 @@
 
 #include "ctx.h"
 #include "life_core.cuh"
+#include "life_multi.cuh"
 
 namespace lifeb200 {
 
@@ -13,15 +14,18 @@ constexpr int kBlock = 256;
 // squeezing to 64 registers, and the ALU pipe goes from 95-96% to 99% busy (tools/ubench_step.cu,
 // profiles/r01h_ubench_step.txt).
 constexpr int kStepBlock = 128;
-// From this many generations per launch the tile is stepped in the row-interleaved layout (one shift
-// per register and generation instead of two, life_core.cuh); the conversions cost about 4 generations.
-constexpr unsigned kInterleaveFrom = 16;
+// Register layouts of the step kernel (lifeb200_set_step_layout; life_core.cuh / life_multi.cuh):
+//   1 = the reference's (rows 0..31 | 32..63): 2 shifts per register and generation, no conversion
+//   2 = even | odd rows: 1 shift per register; 4, 8 = rows by class mod 4 / 8 with 2 / 4 patterns
+//   bit-interleaved per register: 1/2, 1/4 shift per register.  The conversions after the load and before
+//   the store cost about 4 (layout 2) to 14 (layout 8) generations' worth of work, so auto picks by gens.
+constexpr unsigned kInterleaveFrom = 16, kMultiFrom = 96;
 
 // Each warp owns 32/LPP whole patterns; `gens` generations run in registers between one
 // 128-bit vectorised load and one 128-bit vectorised store per 16 bytes of state.
 template <int LPP>
 __global__ void __launch_bounds__(kStepBlock, 1) step_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
-                                                              size_t n, unsigned gens) {
+                                                              size_t n, unsigned gens, bool interleaved) {
   const size_t gid = (size_t)blockIdx.x * kStepBlock + threadIdx.x;
   const size_t p = gid / LPP;
   const int sub = threadIdx.x & (LPP - 1);
@@ -33,7 +37,7 @@ __global__ void __launch_bounds__(kStepBlock, 1) step_kernel(const uint64_t* __r
 #pragma unroll
     for (int w = 0; w < Tile<LPP>::W; w++) t.lo[w] = t.hi[w] = 0;
   }
-  if (gens >= kInterleaveFrom) {  // warp-uniform: many generations pay for the two layout conversions
+  if (interleaved) {  // uniform over the launch: many generations pay for the two layout conversions
     t.interleave();
 #pragma unroll 1
     for (unsigned g = 0; g < gens; g++) t.template step<true>(sub);
@@ -43,6 +47,43 @@ __global__ void __launch_bounds__(kStepBlock, 1) step_kernel(const uint64_t* __r
     for (unsigned g = 0; g < gens; g++) t.template step<false>(sub);
   }
   if (valid) t.store(out + p * kN, sub);
+}
+
+// P = M/2 patterns per group of 8 lanes in the row-class layout of life_multi.cuh.
+template <int M>
+__global__ void __launch_bounds__(kStepBlock, 1) step_kernel_x(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
+                                                                size_t n, unsigned gens) {
+  constexpr int P = M / 2;
+  const size_t gid = (size_t)blockIdx.x * kStepBlock + threadIdx.x;
+  const size_t p0 = (gid >> 3) * P;  // first pattern of this lane group
+  const int sub = threadIdx.x & 7;   // this lane owns columns 8*sub .. 8*sub+7 of all P patterns
+  TileX<M> t;
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    uint64_t wa[P], wb[P];
+#pragma unroll
+    for (int s = 0; s < P; s++) {
+      uint4 v = make_uint4(0, 0, 0, 0);  // groups past the end step empty patterns (they still shuffle)
+      if (p0 + s < n) v = __ldg(reinterpret_cast<const uint4*>(in + (p0 + s) * kN + sub * 8 + c));
+      wa[s] = ((uint64_t)v.y << 32) | v.x;
+      wb[s] = ((uint64_t)v.w << 32) | v.z;
+    }
+    t.pack(c, wa);
+    t.pack(c + 1, wb);
+  }
+#pragma unroll 1
+  for (unsigned g = 0; g < gens; g++) t.step(sub);
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    uint64_t wa[P], wb[P];
+    t.unpack(c, wa);
+    t.unpack(c + 1, wb);
+#pragma unroll
+    for (int s = 0; s < P; s++)
+      if (p0 + s < n)
+        *reinterpret_cast<uint4*>(out + (p0 + s) * kN + sub * 8 + c) =
+            make_uint4((uint32_t)wa[s], (uint32_t)(wa[s] >> 32), (uint32_t)wb[s], (uint32_t)(wb[s] >> 32));
+  }
 }
 
 template <int LPP>
@@ -116,8 +157,18 @@ int launch_step(lifeb200_ctx* ctx, cudaStream_t st, const uint64_t* in, uint64_t
   // Measured on B200 (profiles/r01h_ubench_step.txt): 8 lanes per pattern (8 words per lane) keeps the ALU
   // pipe busiest when many generations run per launch; with few generations the launch is HBM-bound and
   // 16 lanes per pattern (32 contiguous bytes per lane) coalesces best.
-  int lpp = ctx->lpp ? ctx->lpp : (gens >= 8 ? 8 : 16);
-  LIFEB200_DISPATCH_LPP(lpp, (step_kernel<LPP><<<(unsigned)((n * (size_t)LPP + kStepBlock - 1) / kStepBlock), kStepBlock, 0, st>>>(in, out, n, gens)));
+  int layout = ctx->step_layout;
+  if (layout == 0) layout = (gens >= kMultiFrom && ctx->lpp == 0) ? 8 : gens >= kInterleaveFrom ? 2 : 1;
+  if (layout >= 4) {
+    const size_t groups = (n + layout / 2 - 1) / (layout / 2);
+    const unsigned grid = (unsigned)((groups * 8 + kStepBlock - 1) / kStepBlock);
+    if (layout == 8) step_kernel_x<8><<<grid, kStepBlock, 0, st>>>(in, out, n, gens);
+    else step_kernel_x<4><<<grid, kStepBlock, 0, st>>>(in, out, n, gens);
+  } else {
+    int lpp = ctx->lpp ? ctx->lpp : (gens >= 8 ? 8 : 16);
+    LIFEB200_DISPATCH_LPP(lpp, (step_kernel<LPP><<<(unsigned)((n * (size_t)LPP + kStepBlock - 1) / kStepBlock), kStepBlock, 0, st>>>(
+                                   in, out, n, gens, layout == 2)));
+  }
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }

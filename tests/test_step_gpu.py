@@ -207,3 +207,32 @@ def test_translation_equivariance(engine, port):
     a = dev_step(engine, moved, 100)
     b = np.stack([port.moved(s, 13, -27) for s in dev_step(engine, soups, 100)])
     assert (a == b).all()
+
+
+@pytest.mark.parametrize("layout", [1, 2, 4, 8])
+def test_step_every_register_layout(engine, port, layout):
+    """The register layout of the step kernel (reference, even/odd rows, 2 or 4 patterns bit-interleaved per
+    register) never shows: same bits for ragged batch sizes around the 2- and 4-pattern group size, both soup
+    distributions, odd generation counts, in place and out of place."""
+    engine.set_step_layout(layout)
+    try:
+        for n, gens, dist in ((1, 1, 0), (2, 3, 1), (3, 17, 0), (5, 64, 1), (63, 33, 0), (130, 7, 0), (1027, 100, 0)):
+            soups = port.soup(900 + n, n, SEED, dist)
+            assert (engine.step_batch_host(soups, gens) == port.step_batch(soups, gens)).all(), (layout, n, gens)
+        g = golden("rpentomino.npz")
+        want = {int(k): g["states"][i] for i, k in enumerate(g["gens"])}
+        for gen in (1, 2, 3, 10, 64, 100, 256, 1000, 1024):
+            assert (engine.step_batch_host(want[0][None, :], gen)[0] == want[gen]).all(), (layout, gen)
+        soups = np.ascontiguousarray(port.soup(5, 77, SEED, 0))
+        d = engine.malloc(soups.nbytes)
+        try:
+            engine.h2d(d, soups)
+            engine.step_batch_dev(d, d, 77, 129)  # in place
+            out = np.empty_like(soups)
+            engine.d2h(out, d)
+            engine.sync()
+        finally:
+            engine.free(d)
+        assert (out == port.step_batch(soups, 129)).all()
+    finally:
+        engine.set_step_layout(0)
