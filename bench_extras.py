@@ -133,7 +133,7 @@ def config5_survey(eng, p_int):
     cells = n * 4096.0 * gens
     return {"workload": f"config5 (1/16 scale): {n} on-device soups x {gens} gens, active iff state(G) != state(G-2)", "s": dt,
             "value": cells / dt / 1e9, "unit": "Gcell/s", "active": int(len(hits)), "pop_sum": int(pop_sum),
-            "hash_xor": f"{int(hash_xor):016x}", "int_pipe_frac_executed": cells * (9.5 / 32.0) / dt / p_int,
+            "hash_xor": f"{int(hash_xor):016x}", "int_pipe_frac_executed": cells * (7.75 / 32.0) / dt / p_int,
             "timing": "wall clock around the host-facing call, hits downloaded and sorted"}
 
 

@@ -6,6 +6,7 @@
 
 #include "ctx.h"
 #include "life_core.cuh"
+#include "life_multi.cuh"
 
 namespace lifeb200 {
 
@@ -47,11 +48,16 @@ __device__ __forceinline__ void append_hit(bool emit, uint64_t id, uint32_t a, u
 }
 
 template <int LPP>
-__device__ __forceinline__ void run_match(Tile<LPP>& t, const Tile<LPP>& wm, const Tile<LPP>& m, int sub, int lane,
+__device__ __forceinline__ void run_match(Tile<LPP>& t, Tile<LPP>& wm, Tile<LPP>& m, int sub, int lane,
                                           unsigned gens, unsigned stable_interval, Recovery& r) {
+  // even/odd row registers for the whole run (one shift per register and generation, life_core.cuh);
+  // Contains is bit-position-wise, so the target planes are converted once and nothing is converted back
+  t.interleave();
+  wm.interleave();
+  m.interleave();
 #pragma unroll 1
   for (unsigned g = 1; g <= gens; g++) {
-    t.step(sub);
+    t.template step<true>(sub);
     uint32_t d = t.target_diff(wm, m);
     bool mismatch = group_any<LPP>(d != 0, lane);
     r.observe(mismatch, g, stable_interval);
@@ -197,17 +203,85 @@ __global__ void __launch_bounds__(kBlockM, 1) survey_kernel(uint64_t first_id, s
     uint64_t v = valid ? soup_word(seed, id, sub * W + w, dist) : 0ULL;
     t.lo[w] = (uint32_t)v; t.hi[w] = (uint32_t)(v >> 32);
   }
+  t.interleave();  // even/odd row registers; ==, GetPop are layout-blind, the fold needs the words back
+#pragma unroll 1
+  for (unsigned g = 0; g + 2 < gens; g++) t.template step<true>(sub);
+  before = t;
+  t.template step<true>(sub);
+  t.template step<true>(sub);
+  const bool active = group_any<LPP>(t.xor_diff(before) != 0, lane);
+  const uint32_t pop = group_sum<LPP>(t.pop());
+  t.deinterleave();
+  const uint64_t f = group_fold<LPP>(t, sub);
+  const bool leader = valid && sub == 0;
+  block_accumulate(leader ? pop : 0u, leader ? splitmix64(f + id) : 0ULL, pop_sum, hash_xor);
+  append_hit(leader && active, id, pop, 0u, hits, cap, n_hits);
+}
+
+// The same survey with P = M/2 soups per group of 8 lanes in the row-class layout (life_multi.cuh).
+template <int M>
+__global__ void __launch_bounds__(128, 1) survey_kernel_x(uint64_t first_id, size_t n, uint64_t seed, int dist, unsigned gens,
+                                                          lifeb200_hit* hits, size_t cap, unsigned long long* n_hits,
+                                                          unsigned long long* pop_sum, unsigned long long* hash_xor) {
+  constexpr int P = M / 2;
+  const size_t gid = (size_t)blockIdx.x * 128 + threadIdx.x;
+  const size_t p0 = (gid >> 3) * P;
+  const int lane = threadIdx.x & 31, sub = threadIdx.x & 7;
+  TileX<M> t, before;
+#pragma unroll
+  for (int c = 0; c < 8; c++) {
+    uint64_t w[P];
+#pragma unroll
+    for (int s = 0; s < P; s++) w[s] = (p0 + s < n) ? soup_word(seed, first_id + p0 + s, sub * 8 + c, dist) : 0ULL;
+    t.pack(c, w);
+  }
 #pragma unroll 1
   for (unsigned g = 0; g + 2 < gens; g++) t.step(sub);
   before = t;
   t.step(sub);
   t.step(sub);
-  const bool active = group_any<LPP>(t.xor_diff(before) != 0, lane);
-  const uint32_t pop = group_sum<LPP>(t.pop());
-  const uint64_t f = group_fold<LPP>(t, sub);
-  const bool leader = valid && sub == 0;
-  block_accumulate(leader ? pop : 0u, leader ? splitmix64(f + id) : 0ULL, pop_sum, hash_xor);
-  append_hit(leader && active, id, pop, 0u, hits, cap, n_hits);
+  // per soup s: its cells are the bits j*P + s of every register
+  uint32_t diff = 0, pop[P];
+#pragma unroll
+  for (int s = 0; s < P; s++) pop[s] = 0;
+#pragma unroll
+  for (int c = 0; c < 8; c++)
+#pragma unroll
+    for (int k = 0; k < M; k++) {
+      diff |= t.r[c][k] ^ before.r[c][k];
+#pragma unroll
+      for (int s = 0; s < P; s++) pop[s] += __popc(t.r[c][k] & ((0xFFFFFFFFu / ((1u << P) - 1u)) << s));
+    }
+  uint64_t f[P];
+#pragma unroll
+  for (int s = 0; s < P; s++) f[s] = 0;
+#pragma unroll
+  for (int c = 0; c < 8; c++) {
+    uint64_t w[P];
+    t.unpack(c, w);
+#pragma unroll
+    for (int s = 0; s < P; s++) f[s] ^= splitmix64(w[s] + (uint64_t)(sub * 8 + c) * kFoldK);
+  }
+  // lane `sub` of the group reports soup s = sub (sub < P)
+  uint32_t my_pop = 0, my_diff = 0;
+  uint64_t my_f = 0;
+#pragma unroll
+  for (int s = 0; s < P; s++) {
+    uint32_t d = diff & ((0xFFFFFFFFu / ((1u << P) - 1u)) << s), q = pop[s];
+    uint64_t h = f[s];
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+      d |= __shfl_xor_sync(0xffffffffu, d, o, 32);
+      q += __shfl_xor_sync(0xffffffffu, q, o, 32);
+      h ^= __shfl_xor_sync(0xffffffffu, h, o, 32);
+    }
+    if (sub == s) { my_pop = q; my_diff = d; my_f = h; }
+  }
+  (void)lane;
+  const bool leader = sub < P && p0 + sub < n;
+  const uint64_t id = first_id + p0 + sub;
+  block_accumulate(leader ? my_pop : 0u, leader ? splitmix64(my_f + id) : 0ULL, pop_sum, hash_xor);
+  append_hit(leader && my_diff != 0, id, my_pop, 0u, hits, cap, n_hits);
 }
 
 template <int LPP>
@@ -351,10 +425,19 @@ int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_
   if (cap) LIFEB200_CUDA(cudaMalloc(&d_hits, cap * sizeof(lifeb200_hit)));
   auto body = [&]() -> int {
     LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
-    int lpp = survey_lpp(ctx);
-    LIFEB200_DISPATCH_LPP(lpp, (survey_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
-                                   first_id, n, seed, dist, gens, d_hits, cap, ctx->d_counters + 0, ctx->d_counters + 2,
-                                   ctx->d_counters + 3)));
+    // many generations: 4 soups per lane group in the row-class layout (life_multi.cuh), unless the caller
+    // pinned the lane grouping or the layout
+    const bool multi = gens >= 96 && ctx->lpp == 0 && (ctx->step_layout == 0 || ctx->step_layout == 8);
+    if (multi) {
+      const size_t groups = (n + 3) / 4;
+      survey_kernel_x<8><<<(unsigned)((groups * 8 + 127) / 128), 128, 0, ctx->stream>>>(
+          first_id, n, seed, dist, gens, d_hits, cap, ctx->d_counters + 0, ctx->d_counters + 2, ctx->d_counters + 3);
+    } else {
+      int lpp = survey_lpp(ctx);
+      LIFEB200_DISPATCH_LPP(lpp, (survey_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
+                                     first_id, n, seed, dist, gens, d_hits, cap, ctx->d_counters + 0, ctx->d_counters + 2,
+                                     ctx->d_counters + 3)));
+    }
     LIFEB200_LAUNCHED(ctx);
     LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 4 * sizeof(unsigned long long),
                                   cudaMemcpyDeviceToHost, ctx->stream));

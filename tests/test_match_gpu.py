@@ -119,6 +119,17 @@ def test_soup_survey_vs_oracle(engine, port):
         assert (ps, hx) == (ps_o, hx_o)
 
 
+def test_soup_survey_default_path_four_soups_per_group(engine, port):
+    """gens >= 96 with no pinned lane grouping takes survey_kernel_x (4 soups bit-interleaved per lane group):
+    ragged counts around the group size, both distributions, huge first ids."""
+    for (first, n, dist, gens) in [(0, 1, 0, 96), (3, 2, 1, 100), (9, 3, 0, 97), (1 << 40, 5, 0, 128), (77, 1023, 0, 200),
+                                   (0, 4099, 1, 96)]:
+        hits, ps, hx = engine.soup_survey(first, n, SEED, dist, gens, cap=n)
+        ids, pops, ps_o, hx_o = port.survey(first, n, SEED, dist, gens, n)
+        assert (hits["id"] == ids).all() and (hits["g_first_false"] == pops).all(), (first, n, gens)
+        assert (ps, hx) == (ps_o, hx_o), (first, n, gens)
+
+
 def test_fold_matches_oracle(engine, port):
     soups = port.soup(50, 999, SEED)
     d = engine.malloc(soups.nbytes)
