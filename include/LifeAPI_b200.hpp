@@ -177,6 +177,57 @@ struct alignas(64) LifeState {
     InteractionCountsAndNext(out1, out2, outMore, next);
   }
 
+  // ---- locating patterns on the torus (LifeAPI.hpp:427-442,789-795,1066-1095,1293-1370), on the GPU ----
+  [[nodiscard]] LifeState Mirrored() const {  // (x, y) -> (-x, -y): FlipX, FlipY, Move(1, 1)
+    LifeState r;
+    for (int i = 0; i < N; i++) {
+      uint64_t v = state[(N - i) & 63], b = 0;
+      for (int k = 0; k < 64; k++) b |= ((v >> k) & 1ULL) << (63 - k);
+      r.state[i] = std::rotl(b, 1);
+    }
+    return r;
+  }
+  [[nodiscard]] LifeState Convolve(const LifeState& other) const {
+    LifeState r;
+    lifeb200::Check(lifeb200_convolve_batch_host(lifeb200::DefaultContext(), state, 1, other.state, 1, r.state, 1), "Convolve");
+    return r;
+  }
+  [[nodiscard]] LifeState MatchLive(const LifeState& live) const {
+    LifeState r;
+    lifeb200::Check(lifeb200_match_batch_host(lifeb200::DefaultContext(), state, 1, live.state, nullptr, 1, LIFEB200_MATCH_LIVE, r.state), "MatchLive");
+    return r;
+  }
+  [[nodiscard]] LifeState MatchLiveAndDead(const LifeState& live, const LifeState& dead) const {
+    LifeState r;
+    lifeb200::Check(lifeb200_match_batch_host(lifeb200::DefaultContext(), state, 1, live.state, dead.state, 1, LIFEB200_MATCH_LIVE_AND_DEAD, r.state), "MatchLiveAndDead");
+    return r;
+  }
+  [[nodiscard]] LifeState Match(const LifeState& live) const {  // dead = live.GetBoundary()
+    LifeState r;
+    lifeb200::Check(lifeb200_match_batch_host(lifeb200::DefaultContext(), state, 1, live.state, nullptr, 1, LIFEB200_MATCH_BOUNDARY, r.state), "Match");
+    return r;
+  }
+  [[nodiscard]] LifeState Match(const LifeTarget& target) const;  // LifeTarget.hpp:53-54 (defined below)
+  [[nodiscard]] LifeState InteractionOffsets(const LifeState& other) const {
+    LifeState r;
+    lifeb200::Check(lifeb200_interaction_offsets_host(lifeb200::DefaultContext(), state, 1, other.state, 1, r.state, 1), "InteractionOffsets");
+    return r;
+  }
+
+  // ---- RLE output (Parsing.hpp:8-66,198-202); written from cell (32, 32), as the reference does ----
+  [[nodiscard]] std::string RLE() const {
+    std::string s(1024, '\0');
+    size_t len = 0;
+    int rc = lifeb200_rle(state, s.data(), s.size(), &len);
+    if (rc == LIFEB200_E_OVERFLOW) {
+      s.assign(len + 1, '\0');
+      rc = lifeb200_rle(state, s.data(), s.size(), &len);
+    }
+    lifeb200::Check(rc, "RLE");
+    s.resize(len);
+    return s;
+  }
+
   bool Contains(const LifeTarget& target) const;  // LifeTarget.hpp:44-51 (defined below)
   bool Contains(const LifeState& pat) const { return (*this & pat) == pat; }                 // :388-397
   bool AreDisjoint(const LifeState& pat) const { return (*this & pat).IsEmpty(); }          // :377-386
@@ -192,6 +243,12 @@ struct LifeTarget {
   [[nodiscard]] LifeTarget Moved(std::pair<int, int> v) const { return LifeTarget(wanted.Moved(v.first, v.second), unwanted.Moved(v.first, v.second)); }
 };
 static_assert(sizeof(LifeTarget) == 1024, "LifeTarget layout (LifeTarget.hpp:5-7)");
+
+inline LifeState LifeState::Match(const LifeTarget& t) const {
+  LifeState r;
+  lifeb200::Check(lifeb200_match_target_batch_host(lifeb200::DefaultContext(), state, 1, t.wanted.state, 1, r.state), "Match(LifeTarget)");
+  return r;
+}
 
 inline bool LifeState::Contains(const LifeTarget& t) const {
   uint64_t d = 0;
@@ -232,6 +289,25 @@ static_assert(sizeof(NeighbourCount) == 2048, "NeighbourCount layout (NeighbourC
 // LifeHistory.hpp:8-12: passive 4-plane container (no Step in the reference).
 struct LifeHistory {
   LifeState state, history, marked, original;
+  // RLE / Parse in the reference's LifeHistory alphabet (LifeHistory.hpp:25-44,62-93)
+  [[nodiscard]] std::string RLE() const {
+    std::string s(4096, '\0');
+    size_t len = 0;
+    int rc = lifeb200_history_rle(state.state, s.data(), s.size(), &len);
+    if (rc == LIFEB200_E_OVERFLOW) {
+      s.assign(len + 1, '\0');
+      rc = lifeb200_history_rle(state.state, s.data(), s.size(), &len);
+    }
+    lifeb200::Check(rc, "LifeHistory::RLE");
+    s.resize(len);
+    return s;
+  }
+  [[nodiscard]] std::string RLEWHeader() const { return "x = 0, y = 0, rule = LifeHistory\n" + RLE(); }
+  static LifeHistory Parse(const std::string& rle) {
+    LifeHistory h;
+    lifeb200::Check(lifeb200_history_parse_rle(rle.c_str(), h.state.state), "LifeHistory::Parse");
+    return h;
+  }
   // build-defined accumulate step: n times { state.Step(); history |= state; } in one launch
   void StepAccumulate(unsigned n = 1) {
     lifeb200_ctx* ctx = lifeb200::DefaultContext();

@@ -26,7 +26,10 @@ def merge_hits(per_rank: list[np.ndarray]) -> np.ndarray:
     if not parts:
         return np.zeros(0, dtype=HIT_DTYPE)
     allh = np.concatenate(parts)
-    return np.sort(allh, order="id")
+    ids = allh["id"]
+    if len(ids) > 1 and not (ids[1:] >= ids[:-1]).all():  # ranks own ascending id ranges: usually already in order
+        allh = allh[np.argsort(ids, kind="stable")]
+    return allh
 
 
 def gather_hits(hits: np.ndarray, counters: list[int], device=None, group=None):

@@ -23,6 +23,14 @@ void lo_stable_vulnerable(const uint64_t* planes, uint64_t* out);
 void lo_weld_step_n(uint64_t* rec, unsigned gens);
 void lo_interaction_counts(const uint64_t* s, uint64_t* out);
 uint64_t lo_xxh3_512(const uint64_t* s);
+void lo_mirrored(const uint64_t* s, uint64_t* out);
+void lo_convolve(const uint64_t* a, const uint64_t* b, uint64_t* out);
+void lo_match_state(const uint64_t* s, const uint64_t* live, uint64_t* out);
+void lo_match_target(const uint64_t* s, const uint64_t* target, uint64_t* out);
+void lo_match_live_and_dead(const uint64_t* s, const uint64_t* live, const uint64_t* dead, uint64_t* out);
+void lo_interaction_offsets(const uint64_t* a, const uint64_t* b, uint64_t* out);
+size_t lo_rle(const uint64_t* state, char* buf, size_t cap);
+size_t lo_history_rle(const uint64_t* rec, char* buf, size_t cap);
 }
 
 static int failures = 0;
@@ -179,7 +187,64 @@ static void Weld_Hash_Interaction() {
   EXPECT_TRUE(blk.Contains(blk.ToTarget()));
 }
 
+// SURVEY.md 8f rank 4 through the header: Mirrored / Convolve / Match / InteractionOffsets / RLE.
+// Call sites read like the reference's users of these members (LifeAPI.hpp:747-750 AlignWith,
+// tests/InteractionTest.cpp:16-24).
+static void Locate_And_RLE() {
+  std::mt19937_64 rng(77);
+  const LifeState eater = LifeState::Parse("2b2o$bobo$bo$2o!");
+  const LifeState glider = LifeState::Parse("bo$2bo$3o!");
+  for (int it = 0; it < 12; it++) {
+    LifeState soup = RandomState(rng) & RandomState(rng) & RandomState(rng);
+    const int dx = (int)(rng() & 63), dy = (int)(rng() & 63);
+    const LifeState placed = eater.Moved(dx, dy);
+    LifeState s = (soup & ~placed.ZOI()) | placed;
+    LifeState want;
+    lo_mirrored(s.state, want.state);
+    EXPECT_EQ(s.Mirrored(), want);
+    lo_convolve(s.state, glider.state, want.state);
+    EXPECT_EQ(s.Convolve(glider), want);
+    EXPECT_EQ(glider.Convolve(s), want);
+    lo_match_state(s.state, eater.state, want.state);
+    const LifeState found = s.Match(eater);
+    EXPECT_EQ(found, want);
+    EXPECT_TRUE(found.Get((unsigned)dx, (unsigned)dy));  // the planted eater is found where it was put
+    const LifeTarget target(eater);
+    EXPECT_EQ(s.Match(target), found);
+    lo_match_target(s.state, target.wanted.state, want.state);
+    EXPECT_EQ(s.Match(target), want);
+    lo_match_live_and_dead(s.state, eater.state, glider.state, want.state);
+    EXPECT_EQ(s.MatchLiveAndDead(eater, glider), want);
+    lo_interaction_offsets(eater.state, soup.state, want.state);
+    EXPECT_EQ(eater.InteractionOffsets(soup), want);
+    char buf[1 << 15];
+    EXPECT_EQ(s.RLE(), std::string(buf, lo_rle(s.state, buf, sizeof buf)));
+    LifeHistory h;
+    h.state = s; h.history = soup.Moved(1, 0) & ~s; h.marked = placed;  // letters A, B, C only: all of them parse back
+    EXPECT_EQ(h.RLE(), std::string(buf, lo_history_rle(h.state.state, buf, sizeof buf)));
+    const LifeHistory back = LifeHistory::Parse(h.RLE());
+    EXPECT_EQ(back.state, s.Moved(32, 32));  // RLE is written from cell (32, 32): a half-torus shift
+    EXPECT_EQ(back.history, h.history.Moved(32, 32));
+    EXPECT_EQ(back.marked, placed.Moved(32, 32));
+  }
+  // glider x eater: overlapping offsets are always reported, offsets whose zones of influence are disjoint never
+  const LifeState offs = eater.InteractionOffsets(glider);
+  int checked = 0;
+  for (int x = 0; x < 64; x += 3)
+    for (int y = 0; y < 64; y += 5) {
+      const LifeState moved = glider.Moved(x, y);
+      if (!(eater & moved).IsEmpty()) EXPECT_TRUE(offs.Get((unsigned)x, (unsigned)y));
+      if ((eater.ZOI() & moved.ZOI()).IsEmpty()) {
+        EXPECT_TRUE(!offs.Get((unsigned)x, (unsigned)y));
+        EXPECT_EQ((eater | moved).Stepped(), eater.Stepped() | moved.Stepped());  // and they really evolve independently
+      }
+      checked++;
+    }
+  EXPECT_TRUE(checked > 200);
+}
+
 int main() {
+  Locate_And_RLE();
   Weld_Hash_Interaction();
   Stable_And_History();
   StepAltTest_Random();
