@@ -70,12 +70,25 @@ def config3_unknown_step(eng, p_int):
         eng.sync()
         d_o = eng.malloc(n * 512)
         ms = _time(eng, lambda: eng.unknown_step_batch_dev(d_s, d_u, d_t, d_o, n, gens))
+        eng.set_three_valued_path(1)
+        ms_lit = _time(eng, lambda: eng.unknown_step_batch_dev(d_s, d_u, d_t, d_o, n, gens))
+        eng.set_three_valued_path(0)
+        long_gens = 256
+        ms_long = _time(eng, lambda: eng.unknown_step_batch_dev(d_s, d_u, d_t, d_o, n, long_gens))
         eng.free(d_o)
         cells = n * 4096.0 * gens
         out = {"workload": f"config3: {n} partial patterns x {gens} three-valued generations", "ms": ms,
                "value": cells / (ms * 1e-3) / 1e9, "unit": "Gcell/s",
                "int_pipe_frac": cells * (40.0 / 32.0) / (ms * 1e-3) / p_int,
-               "algorithmic": "40 int-pipe instr per 32 cells per generation (DESIGN.md 3.3)"}
+               "algorithmic": "40 int-pipe instr per 32 cells per generation: two NeighbourCounts + the 18-LUT cover (DESIGN.md 3.3)",
+               "executed": "26 per 32 cells per generation (22 LOP3 + 4 SHF): two B3/S23 selects on state and state|unknown, "
+                           "csrc/life_three.cuh; planes are disjoint, so every warp takes that path",
+               "pipe_utilisation": cells * (26.0 / 32.0) / (ms * 1e-3) / p_int,
+               "literal_cover": {"ms": ms_lit, "value": cells / (ms_lit * 1e-3) / 1e9, "unit": "Gcell/s",
+                                 "what": "same launch forced through the fragment text (lifeb200_set_three_valued_path 1)"},
+               "long_run": {"generations": long_gens, "ms": ms_long, "value": n * 4096.0 * long_gens / (ms_long * 1e-3) / 1e9,
+                            "unit": "Gcell/s", "executed": "24 per 32 cells per generation (row-interleaved registers)",
+                            "pipe_utilisation": n * 4096.0 * long_gens * (24.0 / 32.0) / (ms_long * 1e-3) / p_int}}
         ref = _cpu_ref()
         if ref is not None:
             m = 1 << 16

@@ -143,7 +143,13 @@ int lifeb200_fold_dev(lifeb200_ctx* ctx, const uint64_t* patterns, size_t n, uin
  * LifeStable.hpp:429-469 uses for stable_simple.hpp: on = NeighbourCount(state), unk =
  * NeighbourCount(unknown) (3x3 sums INCLUDING the centre), per word the cover maps
  * (current_unknown, current_on, on2..on0, unk3..unk0) -> (naive_next_unknown, naive_next_on).
- * state / unknown are separate plane arrays of n x 512 B; out may alias in.  gens may be 0. */
+ * state / unknown are separate plane arrays of n x 512 B; out may alias in.  gens may be 0.
+ * The result is the cover's on every input.  Patterns that keep the LifeStable invariant
+ * state & unknown == 0 (LifeStable.hpp:220-221) are stepped through an equivalent two-select form
+ * (22 instead of 36 LUTs per 32 cells, csrc/life_three.cuh); overlapping planes -- the cover's
+ * don't-care rows -- go through the fragment text itself.  lifeb200_set_three_valued_path(ctx, 1)
+ * sends everything through the fragment text (0 restores the default); results never depend on it. */
+int lifeb200_set_three_valued_path(lifeb200_ctx* ctx, int path);
 int lifeb200_unknown_step_batch_dev(lifeb200_ctx* ctx, const uint64_t* state_in, const uint64_t* unknown_in,
                                     uint64_t* state_out, uint64_t* unknown_out, size_t n, unsigned gens);
 int lifeb200_unknown_step_batch_host(lifeb200_ctx* ctx, const uint64_t* state_in, const uint64_t* unknown_in,

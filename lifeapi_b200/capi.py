@@ -57,6 +57,7 @@ SIGNATURES = {
                                        C.POINTER(C.c_int), C.POINTER(C.c_size_t)]),
     "lifeb200_set_lanes_per_pattern": (C.c_int, [_vp, C.c_int]),
     "lifeb200_set_step_layout": (C.c_int, [_vp, C.c_int]),
+    "lifeb200_set_three_valued_path": (C.c_int, [_vp, C.c_int]),
     "lifeb200_malloc": (C.c_int, [_vp, C.POINTER(_vp), C.c_size_t]),
     "lifeb200_free": (C.c_int, [_vp, _vp]),
     "lifeb200_host_alloc": (C.c_int, [_vp, C.POINTER(_vp), C.c_size_t]),
@@ -186,6 +187,9 @@ class Engine:
 
     def set_step_layout(self, layout: int) -> None:
         self._check(self.lib.lifeb200_set_step_layout(self._h, layout))
+
+    def set_three_valued_path(self, path: int) -> None:
+        self._check(self.lib.lifeb200_set_three_valued_path(self._h, path))
 
     def device_info(self) -> dict:
         sm, ma, mi, khz, mem = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_size_t()

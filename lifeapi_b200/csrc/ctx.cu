@@ -140,6 +140,13 @@ int lifeb200_set_step_layout(lifeb200_ctx* ctx, int layout) {
   return LIFEB200_OK;
 }
 
+int lifeb200_set_three_valued_path(lifeb200_ctx* ctx, int path) {
+  if (!ctx) return set_error(LIFEB200_E_ARG, "null context");
+  if (path != 0 && path != 1) return set_error(LIFEB200_E_ARG, "three-valued path must be 0 (auto) or 1 (literal cover), got %d", path);
+  ctx->unknown_literal = path;
+  return LIFEB200_OK;
+}
+
 int lifeb200_set_lanes_per_pattern(lifeb200_ctx* ctx, int lpp) {
   if (!ctx) return set_error(LIFEB200_E_ARG, "null context");
   if (lpp != 0 && lpp != 1 && lpp != 2 && lpp != 4 && lpp != 8 && lpp != 16 && lpp != 32)

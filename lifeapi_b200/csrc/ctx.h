@@ -28,6 +28,7 @@ struct lifeb200_ctx {
   size_t total_mem = 0;
   int lpp = 0;  // 0 = default
   int step_layout = 0;  // 0 = auto, 1 = reference, 2 / 4 / 8 = row classes per column (lifeb200_set_step_layout)
+  int unknown_literal = 0;  // 1 = three-valued step always through the literal cover (lifeb200_set_three_valued_path)
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;  // == own_stream unless lifeb200_set_stream
   cudaEvent_t ev_start = nullptr, ev_stop = nullptr;

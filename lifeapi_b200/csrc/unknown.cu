@@ -11,6 +11,7 @@
 #include "ctx.h"
 #include "generated/circuits.cuh"
 #include "life_core.cuh"
+#include "life_three.cuh"
 
 namespace lifeb200 {
 
@@ -33,12 +34,17 @@ __device__ __forceinline__ void unknown_step_tile(Tile<LPP>& s, Tile<LPP>& u, in
   }
 }
 
-template <int LPP>
+// A warp whose patterns all keep state & unknown == 0 (every reachable LifeStable / LifeHistory input)
+// steps through the two-select form of life_three.cuh, row-interleaved when IL; a warp that sees
+// overlapping planes is outside the generator's domain and follows the fragment text literally
+// (unknown_step_tile), so the result is the cover's on EVERY input.  The choice is per warp because
+// both paths shuffle with a full mask.
+template <int LPP, bool IL>
 __global__ void __launch_bounds__(kBlockU, 1) unknown_step_kernel(const uint64_t* __restrict__ state_in,
                                                                const uint64_t* __restrict__ unknown_in,
                                                                uint64_t* __restrict__ state_out,
                                                                uint64_t* __restrict__ unknown_out, size_t n,
-                                                               unsigned gens) {
+                                                               unsigned gens, int force_literal) {
   const size_t gid = (size_t)blockIdx.x * kBlockU + threadIdx.x;
   const size_t p = gid / LPP;
   const int sub = threadIdx.x & (LPP - 1);
@@ -51,8 +57,18 @@ __global__ void __launch_bounds__(kBlockU, 1) unknown_step_kernel(const uint64_t
 #pragma unroll
     for (int w = 0; w < Tile<LPP>::W; w++) s.lo[w] = s.hi[w] = u.lo[w] = u.hi[w] = 0;
   }
+  uint32_t both = 0;
+#pragma unroll
+  for (int w = 0; w < Tile<LPP>::W; w++) both |= (s.lo[w] & u.lo[w]) | (s.hi[w] & u.hi[w]);
+  if (__any_sync(0xffffffffu, both != 0 || force_literal)) {
 #pragma unroll 1
-  for (unsigned g = 0; g < gens; g++) unknown_step_tile<LPP>(s, u, sub);
+    for (unsigned g = 0; g < gens; g++) unknown_step_tile<LPP>(s, u, sub);
+  } else {
+    if constexpr (IL) { s.interleave(); u.interleave(); }
+#pragma unroll 1
+    for (unsigned g = 0; g < gens; g++) three_valued_step<LPP, IL>(s, u, sub);
+    if constexpr (IL) { s.deinterleave(); u.deinterleave(); }
+  }
   if (valid) {
     s.store(state_out + p * kN, sub);
     u.store(unknown_out + p * kN, sub);
@@ -90,14 +106,32 @@ __global__ void __launch_bounds__(kBlockU, 1) history_step_kernel(uint64_t* __re
 
 static inline unsigned grid_u(size_t n, int lpp) { return (unsigned)((n * (size_t)lpp + kBlockU - 1) / kBlockU); }
 
-// 10 count/plane tiles live at once: keep W <= 4
-static inline int unknown_lpp(const lifeb200_ctx* ctx) { return std::max(16, effective_lpp(ctx)); }
+// lanes per pattern: 16 by default (W = 4 words per lane; the literal path keeps 10 count/plane tiles
+// live at once), 4 / 8 / 32 on request
+static inline int unknown_lpp(const lifeb200_ctx* ctx) { return ctx->lpp == 0 ? 16 : std::max(4, ctx->lpp); }
+// row-interleaving costs about 17 integer instructions per register each way and saves 2 of 26 per
+// generation; lifeb200_set_step_layout(1) pins the reference layout, (2) the interleaved one
+constexpr unsigned kUnknownInterleaveFrom = 40;
+
+template <bool IL>
+static int launch_unknown_step_il(cudaStream_t st, int lpp, const uint64_t* si, const uint64_t* ui, uint64_t* so, uint64_t* uo,
+                                  size_t n, unsigned gens, int literal) {
+  switch (lpp) {
+    case 4: unknown_step_kernel<4, IL><<<grid_u(n, 4), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
+    case 8: unknown_step_kernel<8, IL><<<grid_u(n, 8), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
+    case 16: unknown_step_kernel<16, IL><<<grid_u(n, 16), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
+    default: unknown_step_kernel<32, IL><<<grid_u(n, 32), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
+  }
+  return LIFEB200_OK;
+}
 
 int launch_unknown_step(lifeb200_ctx* ctx, cudaStream_t st, const uint64_t* si, const uint64_t* ui, uint64_t* so,
                         uint64_t* uo, size_t n, unsigned gens) {
   if (n == 0) return LIFEB200_OK;
-  int lpp = unknown_lpp(ctx);
-  LIFEB200_DISPATCH_LPP(lpp, (unknown_step_kernel<LPP><<<grid_u(n, LPP), kBlockU, 0, st>>>(si, ui, so, uo, n, gens)));
+  const int lpp = unknown_lpp(ctx);
+  const bool il = ctx->step_layout == 0 ? gens >= kUnknownInterleaveFrom : ctx->step_layout >= 2;
+  if (il) launch_unknown_step_il<true>(st, lpp, si, ui, so, uo, n, gens, ctx->unknown_literal);
+  else launch_unknown_step_il<false>(st, lpp, si, ui, so, uo, n, gens, ctx->unknown_literal);
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }

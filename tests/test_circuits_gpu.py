@@ -18,18 +18,59 @@ def test_unknown_step_golden(engine):
         assert (s == g["next_state"][i]).all() and (u == g["next_unknown"][i]).all()
 
 
-@pytest.mark.parametrize("lpp", (0, 16, 32))
+@pytest.mark.parametrize("layout", (0, 1, 2))
+@pytest.mark.parametrize("lpp", (0, 4, 8, 16, 32))
 @pytest.mark.parametrize("n", (1, 5, 33, 1000))
-def test_unknown_step_vs_oracle(engine, port, lpp, n):
+def test_unknown_step_vs_oracle(engine, port, lpp, n, layout):
     engine.set_lanes_per_pattern(lpp)
+    engine.set_step_layout(layout)
     try:
         st, un = three_valued_patterns(n, 100 + n, port.soup(9000, n, SEED, 0), port.zoi)
-        for gens in (0, 1, 7):
+        for gens in (0, 1, 7, 41):
             want = port.unknown_step_sop_batch(st, un, gens)
             got = engine.unknown_step_batch_host(st, un, gens)
             assert (got[0] == want[0]).all() and (got[1] == want[1]).all(), (lpp, n, gens)
     finally:
         engine.set_lanes_per_pattern(0)
+        engine.set_step_layout(0)
+
+
+@pytest.mark.parametrize("layout", (1, 2))
+def test_unknown_step_two_select_path_equals_the_cover(engine, port, layout):
+    """The default path steps disjoint planes through two B3/S23 selects (csrc/life_three.cuh) and overlapping
+    ones through the fragment text; lifeb200_set_three_valued_path(1) forces the text for everything.  Both
+    must agree bit for bit: dense unknowns, sparse unknowns, no unknowns, everything unknown, and a batch
+    where every 7th pattern overlaps (so warps holding both kinds take the literal path as a whole)."""
+    n = 4096
+    rng = np.random.default_rng(31)
+    soups = port.soup(0, n, SEED, 0)
+    r = rng.integers(0, 1 << 63, size=(3, n, 64), dtype=np.uint64) << np.uint64(1)
+    un = r[0].copy()
+    un[n // 4: n // 2] &= r[1][n // 4: n // 2] & r[2][n // 4: n // 2]
+    un[n // 2: 3 * n // 4] = 0
+    un[-1] = ~np.uint64(0)
+    st = soups & ~un
+    mixed_st = st.copy()
+    mixed_st[::7] |= un[::7] & r[1][::7]
+    engine.set_step_layout(layout)
+    try:
+        for s_in, u_in in ((st, un), (mixed_st, un)):
+            for gens in (1, 2, 16, 50):
+                engine.set_three_valued_path(1)
+                want = engine.unknown_step_batch_host(s_in, u_in, gens)
+                engine.set_three_valued_path(0)
+                got = engine.unknown_step_batch_host(s_in, u_in, gens)
+                assert (got[0] == want[0]).all() and (got[1] == want[1]).all(), (layout, gens)
+        sel = np.arange(0, n, 61)
+        want = port.unknown_step_sop_batch(mixed_st[sel], un[sel], 16)
+        got = engine.unknown_step_batch_host(mixed_st[sel], un[sel], 16)
+        assert (got[0] == want[0]).all() and (got[1] == want[1]).all()
+    finally:
+        engine.set_three_valued_path(0)
+        engine.set_step_layout(0)
+    from lifeapi_b200 import LifeB200Error
+    with pytest.raises(LifeB200Error):
+        engine.set_three_valued_path(2)
 
 
 def test_unknown_step_dont_care_rows_and_life_limit(engine, port):

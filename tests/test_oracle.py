@@ -335,6 +335,93 @@ def test_pair_shared_rule_luts_exhaustive():
     assert checked == 192
 
 
+def test_three_valued_fast_path_exhaustive():
+    """csrc/life_three.cuh: two B3/S23 selects (on state and on state | unknown) + 3 combining LUTs must equal
+    the reference's unknown_step.hpp cover on EVERY input with disjoint state / unknown planes.  All
+    neighbourhoods are enumerated column-wise: the centre column as raw three-valued cells (27 triples), the
+    two other columns as (count of ON, count of ON-or-UNKNOWN) pairs, once with the centre column as the left
+    and once as the right member of the column pair.  Bit-parallel: one Python int bit per case."""
+    import os
+    import re
+    from conftest import ROOT
+    from lifeapi_b200.bitslicing import emit_cuda as E
+    src = open(os.path.join(ROOT, "lifeapi_b200", "csrc", "life_three.cuh")).read()
+    body = src[src.index("PairCode4 pair_code4("):src.index("template <int LPP, bool IL>")]
+    body = body.replace("kMaj", "0xE8").replace("kOr3", "0xFE")
+    luts = [int(m, 16) for m in re.findall(r"lop3<(0x\w+)>", body)]
+    assert luts == [0x56, 0xBE, 0xE4, 0x92, 0xB2, 0x48, 0xE8, 0xFE, 0x46, 0x92, 0xE8, 0xE2, 0xFE, 0x16, 0x08, 0x47, 0xF8]
+    code_l, left_l, right_l, comb_l = luts[0:4], luts[4:9], luts[9:14], luts[14:17]
+
+    cases = []  # (own column cells [(s,u)]*3, other pair member (cs, ct), far column (cs, ct), own_is_left)
+    others = [(cs, ct) for cs in range(4) for ct in range(cs, 4)]
+    for cells in __import__("itertools").product(((0, 0), (1, 0), (0, 1)), repeat=3):
+        for mate in others:
+            for far in others:
+                for own_is_left in (True, False):
+                    cases.append((cells, mate, far, own_is_left))
+    n = len(cases)
+    assert n == 27 * 10 * 10 * 2
+    full = (1 << n) - 1
+
+    def col(fn):
+        v = 0
+        for i, cse in enumerate(cases):
+            if fn(cse):
+                v |= 1 << i
+        return v
+
+    def lop3(lut, a, b, c):
+        r = 0
+        for k in range(8):
+            if lut >> k & 1:
+                r |= (a if k & 4 else ~a) & (b if k & 2 else ~b) & (c if k & 1 else ~c)
+        return r & full
+
+    def plane_signals(own_cnt, mate_cnt, far_cnt, cell):
+        """own_cnt / mate_cnt / far_cnt: case -> 0..3; returns (alive, A) columns of this plane."""
+        # pair (a, b): a = left member.  own is a when own_is_left else b
+        a = lambda c: own_cnt(c) if c[3] else mate_cnt(c)
+        b = lambda c: mate_cnt(c) if c[3] else own_cnt(c)
+        a0, a1 = col(lambda c: a(c) & 1), col(lambda c: a(c) >> 1)
+        b0, b1 = col(lambda c: b(c) & 1), col(lambda c: b(c) >> 1)
+        c0, c1 = col(lambda c: far_cnt(c) & 1), col(lambda c: far_cnt(c) >> 1)
+        p0 = lop3(code_l[0], a0, b0, b1)
+        p1 = lop3(code_l[1], a1, b1, p0)
+        p2 = lop3(code_l[2], a1, b1, p0)
+        p3 = lop3(code_l[3], a0, b0, p1)
+        l0 = lop3(left_l[0], c1, cell, p2)
+        l1 = lop3(left_l[1], c1, p1, p2)
+        l2 = lop3(left_l[2], c0, p3, l0)
+        la, lalive = lop3(left_l[3], p2, l1, l2), lop3(left_l[4], p2, l1, l2)
+        r0 = lop3(right_l[0], c1, cell, p2)
+        r1 = lop3(right_l[1], c0, p3, r0)
+        r2 = lop3(right_l[2], c1, p1, p2)
+        ra, ralive = lop3(right_l[3], p2, r1, r2), lop3(right_l[4], p2, r1, r2)
+        is_left = col(lambda c: c[3])
+        return (lalive & is_left) | (ralive & ~is_left & full), (la & is_left) | (ra & ~is_left & full)
+
+    s_own = lambda c: sum(x[0] for x in c[0])
+    t_own = lambda c: sum(x[0] | x[1] for x in c[0])
+    cell_s, cell_u = col(lambda c: c[0][1][0]), col(lambda c: c[0][1][1])
+    lo_alive, lo_a = plane_signals(s_own, lambda c: c[1][0], lambda c: c[2][0], cell_s)
+    hi_alive, hi_a = plane_signals(t_own, lambda c: c[1][1], lambda c: c[2][1], cell_s | cell_u)
+    next_on = lop3(comb_l[0], cell_u, lo_alive, hi_alive)
+    x = lop3(comb_l[1], lo_a, lo_alive, hi_alive)
+    next_unknown = lop3(comb_l[2], cell_u, hi_a, x)
+
+    cover = dict((c.name, c) for c, _ in E.load_json())["unknown_step"]
+    on = lambda c: s_own(c) + c[1][0] + c[2][0]
+    unk = lambda c: (t_own(c) - s_own(c)) + (c[1][1] - c[1][0]) + (c[2][1] - c[2][0])
+    named = {"current_unknown": cell_u, "current_on": cell_s}
+    for k in range(4):
+        named[f"on{k}"] = col(lambda c, k=k: on(c) >> k & 1)
+        named[f"unk{k}"] = col(lambda c, k=k: unk(c) >> k & 1)
+    want = dict(zip(cover.outputs, E.eval_sop(cover, [named[i] for i in cover.inputs], full)))
+    assert next_on == want["naive_next_on"]
+    assert next_unknown == want["naive_next_unknown"]
+    assert next_on & next_unknown == 0 and next_on != 0 and next_unknown != 0
+
+
 # ---- 8f next rows ---------------------------------------------------------------------------------
 def test_port_next_rows_golden(port):
     g = golden("next_rows.npz")
