@@ -1,6 +1,7 @@
 // step.cu -- batched LifeState::Step(n) (LifeAPI.hpp:877-881,1196-1216), the soup source,
 // NeighbourCount planes and the integer-pipe microbenchmark, with their C-ABI entry points.
 #include <algorithm>
+#include <vector>
 
 #include "ctx.h"
 #include "life_core.cuh"
@@ -182,22 +183,46 @@ int launch_ncount(lifeb200_ctx* ctx, cudaStream_t st, const uint64_t* in, uint64
 }
 
 // Host-pointer pipeline: chunk c uses slot c % kSlots; each slot's stream runs H2D -> kernel -> D2H,
-// so copies of neighbouring chunks overlap the kernel of the current one.
+// so copies of neighbouring chunks overlap the kernel of the current one.  What stays exposed is the
+// first chunk's upload and the last chunk's download, so a large batch starts and ends with small
+// chunks (4 Ki, then 20 Ki patterns: each still uploads in less time than its predecessor computes)
+// and runs 64 Ki-pattern chunks (32 MiB of state) in between.
+static std::vector<size_t> chunk_plan(size_t n) {
+  constexpr size_t kBig = (size_t)1 << 16, kEdge0 = (size_t)1 << 12, kEdge1 = (size_t)20 << 10;
+  std::vector<size_t> plan;
+  if (n <= kEdge0) {
+    plan.push_back(n);
+  } else if (n < 4 * kBig) {
+    for (size_t off = 0; off < n; off += kBig) plan.push_back(std::min(kBig, n - off));
+  } else {
+    plan.push_back(kEdge0);
+    plan.push_back(kEdge1);
+    for (size_t left = n - 2 * (kEdge0 + kEdge1); left > 0;) {
+      const size_t c = std::min(kBig, left);
+      plan.push_back(c);
+      left -= c;
+    }
+    plan.push_back(kEdge1);
+    plan.push_back(kEdge0);
+  }
+  return plan;
+}
+
 template <class LaunchFn>
 int host_pipeline(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n, size_t in_bytes_per, size_t out_bytes_per,
                   bool out_separate, LaunchFn launch) {
   if (n == 0) return LIFEB200_OK;
-  size_t chunk = std::min<size_t>(n, (size_t)1 << 16);  // 64 Ki patterns = 32 MiB of state
-  if (n <= ((size_t)1 << 12)) chunk = n;
-  size_t nchunks = (n + chunk - 1) / chunk;
-  int used = (int)std::min<size_t>(kSlots, nchunks);
+  const std::vector<size_t> plan = chunk_plan(n);
+  const size_t chunk = *std::max_element(plan.begin(), plan.end());
+  int used = (int)std::min<size_t>(kSlots, plan.size());
   for (int s = 0; s < used; s++) {
     int rc = ensure_slot(ctx, s, chunk * in_bytes_per, out_separate ? chunk * out_bytes_per : 0);
     if (rc) return rc;
   }
-  for (size_t c = 0; c < nchunks; c++) {
+  size_t off = 0;
+  for (size_t c = 0; c < plan.size(); c++) {
     Slot& sl = ctx->slots[c % kSlots];
-    size_t off = c * chunk, cnt = std::min(chunk, n - off);
+    const size_t cnt = plan[c];
     const char* src = reinterpret_cast<const char*>(in) + off * in_bytes_per;
     char* dst = reinterpret_cast<char*>(out) + off * out_bytes_per;
     LIFEB200_CUDA(cudaMemcpyAsync(sl.dbuf, src, cnt * in_bytes_per, cudaMemcpyHostToDevice, sl.stream));
@@ -205,6 +230,7 @@ int host_pipeline(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n
     int rc = launch(sl.stream, reinterpret_cast<const uint64_t*>(sl.dbuf), reinterpret_cast<uint64_t*>(dout), cnt);
     if (rc) return rc;
     LIFEB200_CUDA(cudaMemcpyAsync(dst, dout, cnt * out_bytes_per, cudaMemcpyDeviceToHost, sl.stream));
+    off += cnt;
   }
   for (int s = 0; s < used; s++) LIFEB200_CUDA(cudaStreamSynchronize(ctx->slots[s].stream));
   return LIFEB200_OK;
