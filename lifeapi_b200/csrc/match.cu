@@ -25,6 +25,20 @@ struct Recovery {
       if (++run == stable_interval) { hit = true; done = true; recovered = g + 1 - stable_interval; }
     }
   }
+  // the same transition without branches (selects only), for enumerate_kernel_x: it runs two warps per
+  // scheduler, where a divergent branch is an exposed stall and splits the basic block the scheduler
+  // interleaves.  A call with mismatch = false before any mismatch was seen changes nothing.
+  __device__ __forceinline__ void observe_flat(bool mismatch, unsigned g, unsigned stable_interval) {
+    const bool live = !done, mis = live && mismatch;
+    first_false = (mis && !seen_false) ? g : first_false;
+    seen_false = seen_false || mis;
+    const bool ok = live && !mismatch && seen_false;
+    run = mis ? 0u : run + (ok ? 1u : 0u);
+    const bool fin = ok && run == stable_interval;
+    recovered = fin ? g + 1 - stable_interval : recovered;
+    hit = hit || fin;
+    done = done || fin;
+  }
 };
 
 // Warp-aggregated append: one atomicAdd per warp, hits beyond `cap` are counted but not written.
@@ -153,6 +167,142 @@ __global__ void __launch_bounds__(kBlockM, 1) enumerate_kernel(const uint64_t* _
   }
   run_match<LPP>(t, wm, m, sub, lane, gens, stable_interval, r);
   append_hit(valid && r.hit && sub == 0, id, r.first_false, r.recovered, hits, cap, n_hits);
+}
+
+// The same enumeration with 4 placements per group of 8 lanes in the row-class layout (life_multi.cuh).
+// Ids that differ only in their two low bits share catalyst, projectile and dx and have consecutive dy,
+// so a group owns ids 4q .. 4q+3: one set of table words, four rotations.  All four share the target
+// too; its planes come already packed (every cell replicated into the four pattern bits, built on the
+// host per catalyst).  They do not fit in registers next to the state (64 + 128), so every group parks
+// them in shared memory (64 KiB per CTA) and its lanes read them back each generation: 32 LDS.128, one
+// wavefront each, against ~590 integer instructions.
+// Per generation and register: 7.75 (step) + 1.5 (Contains) integer-pipe instructions instead of 8.5 + 1.5.
+constexpr int kEnumXSmem = 128 * 32 * 16;  // threads x uint4 per thread x 16 B
+
+// OR over the 8 lanes of a group (xor-shuffles with a full mask: __reduce_or_sync with a partial mask
+// compiles to a convergence loop with calls and branches)
+__device__ __forceinline__ uint32_t group8_or(uint32_t v) {
+  v |= __shfl_xor_sync(0xffffffffu, v, 1);
+  v |= __shfl_xor_sync(0xffffffffu, v, 2);
+  v |= __shfl_xor_sync(0xffffffffu, v, 4);
+  return v;
+}
+
+__global__ void __launch_bounds__(128, 1) enumerate_kernel_x(const uint64_t* __restrict__ cat_zoi,
+                                                             const uint64_t* __restrict__ proj,
+                                                             const uint64_t* __restrict__ proj_zoi,
+                                                             const uint32_t* __restrict__ packed_wanted,
+                                                             const uint32_t* __restrict__ packed_mask, unsigned n_proj,
+                                                             uint64_t id_begin, uint64_t id_end, unsigned gens,
+                                                             unsigned stable_interval, lifeb200_hit* hits, size_t cap,
+                                                             unsigned long long* n_hits, unsigned long long* n_skipped) {
+  constexpr int M = 8, P = 4;
+  const uint64_t gid = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+  const uint64_t base = (id_begin & ~3ull) + (gid >> 3) * P;
+  const int lane = threadIdx.x & 31, sub = threadIdx.x & 7, mine = sub & 3;
+  const uint64_t id = base + mine;
+  const bool valid = id >= id_begin && id < id_end;
+  const bool group_live = base < id_end;
+  TileX<M> t;
+  const uint4* wanted4 = nullptr;
+  const uint4* mask4 = nullptr;
+  uint32_t overlap = 0;
+  if (group_live) {
+    const unsigned dy0 = (unsigned)(base & 63u), dx = (unsigned)((base >> 6) & 63u);
+    const uint64_t cg = base >> 12;
+    const unsigned g = (unsigned)(cg % n_proj);
+    const uint64_t c = cg / n_proj;
+    const uint64_t* cz = cat_zoi + c * kN;
+    const uint64_t* pw = proj + (size_t)g * kN;
+    const uint64_t* pz = proj_zoi + (size_t)g * kN;
+    wanted4 = reinterpret_cast<const uint4*>(packed_wanted + (c * kN + sub * 8) * M);
+    mask4 = reinterpret_cast<const uint4*>(packed_mask + (c * kN + sub * 8) * M);
+#pragma unroll
+    for (int col = 0; col < 8; col++) {
+      const int i = sub * 8 + col;
+      const int src = (i - (int)dx) & 63;  // Moved: result[i] = rotl(state[i - x], y)
+      const uint64_t zoi_w = __ldg(cz + i), p_w = __ldg(pw + src), pz_w = __ldg(pz + src);
+      uint64_t w[P];
+#pragma unroll
+      for (int q = 0; q < P; q++) {
+        w[q] = rotl64v(p_w, dy0 + q);
+        const uint64_t ov = zoi_w & rotl64v(pz_w, dy0 + q);
+        overlap |= (ov != 0 ? 1u : 0u) << q;
+      }
+      t.pack(col, w);
+      const uint4 a = __ldg(wanted4 + 2 * col), b = __ldg(wanted4 + 2 * col + 1);
+      t.r[col][0] |= a.x; t.r[col][1] |= a.y; t.r[col][2] |= a.z; t.r[col][3] |= a.w;
+      t.r[col][4] |= b.x; t.r[col][5] |= b.y; t.r[col][6] |= b.z; t.r[col][7] |= b.w;
+    }
+  } else {
+#pragma unroll
+    for (int col = 0; col < 8; col++)
+#pragma unroll
+      for (int k = 0; k < M; k++) t.r[col][k] = 0;
+    wanted4 = reinterpret_cast<const uint4*>(packed_wanted + sub * 8 * M);  // catalyst 0: any valid address
+    mask4 = reinterpret_cast<const uint4*>(packed_mask + sub * 8 * M);
+  }
+  // park the planes: one 4 KiB slice per group, [word][lane of the group] as uint4; groups of a warp that
+  // share the catalyst (all four, except across a catalyst edge) then read the FIRST such group's slice, so
+  // a warp's request is 8 distinct consecutive uint4 = one conflict-free 128-byte wavefront
+  extern __shared__ uint4 parked[];  // [16 groups][32 words][8 lanes]; words 0..15 wanted, 16..31 mask
+  const int grp = threadIdx.x >> 3;
+  {
+    uint4* mine4 = parked + grp * 256 + sub;
+#pragma unroll
+    for (int q = 0; q < 16; q++) {
+      mine4[q * 8] = __ldg(wanted4 + q);
+      mine4[(16 + q) * 8] = __ldg(mask4 + q);
+    }
+  }
+  __syncwarp();
+  int src_grp = grp;
+  {
+    const unsigned long long key = group_live ? (unsigned long long)((base >> 12) / n_proj) : ~0ull;
+#pragma unroll
+    for (int o = 3; o >= 0; o--) {  // lowest group of this warp with my catalyst
+      const unsigned long long other = __shfl_sync(0xffffffffu, key, o * 8);
+      if (other == key) src_grp = (grp & ~3) + o;
+    }
+  }
+  const uint4* planes = parked + src_grp * 256 + sub;
+  const bool skip = (group8_or(overlap) >> mine) & 1u;
+  Recovery r;
+  if (!valid || skip) r.done = true;
+  {
+    unsigned sk = __ballot_sync(0xffffffffu, valid && skip && sub < P);
+    if (lane == 0 && sk) atomicAdd(n_skipped, (unsigned long long)__popc(sk));
+  }
+  // The group-wide OR and the recovery state machine of generation g - 1 sit at the top of iteration g, in
+  // the same basic block as the step, so their shuffle latency hides under it (two warps per scheduler:
+  // nothing else would cover it); the first call sees d_prev = 0 and changes nothing.  The per-register
+  // differences are OR-ed as a tree, not a 32-deep chain.
+  uint32_t d_prev = 0;
+#pragma unroll 1
+  for (unsigned g = 1; g <= gens; g++) {
+    asm volatile("" ::: "memory");  // keep the shared loads inside the loop (hoisted they are 128 registers)
+    const uint32_t all = group8_or(d_prev);  // bit 4j+q set: some cell of placement q differed after g - 1
+    r.observe_flat((all & (0x11111111u << mine)) != 0, g - 1, stable_interval);
+    t.step(sub);
+    uint32_t dc[8];
+#pragma unroll
+    for (int col = 0; col < 8; col++) {
+      const uint4 wa = planes[(2 * col) * 8], wb = planes[(2 * col + 1) * 8];
+      const uint4 ma = planes[(16 + 2 * col) * 8], mb = planes[(17 + 2 * col) * 8];
+      const uint32_t x0 = lop3<kAndXor>(t.r[col][0], ma.x, wa.x), x1 = lop3<kAndXor>(t.r[col][1], ma.y, wa.y);
+      const uint32_t x2 = lop3<kAndXor>(t.r[col][2], ma.z, wa.z), x3 = lop3<kAndXor>(t.r[col][3], ma.w, wa.w);
+      const uint32_t x4 = lop3<kAndXor>(t.r[col][4], mb.x, wb.x), x5 = lop3<kAndXor>(t.r[col][5], mb.y, wb.y);
+      const uint32_t x6 = lop3<kAndXor>(t.r[col][6], mb.z, wb.z), x7 = lop3<kAndXor>(t.r[col][7], mb.w, wb.w);
+      dc[col] = lop3<kOr3>(lop3<kOr3>(x0, x1, x2), lop3<kOr3>(x3, x4, x5), x6 | x7);
+    }
+    d_prev = lop3<kOr3>(lop3<kOr3>(dc[0], dc[1], dc[2]), lop3<kOr3>(dc[3], dc[4], dc[5]), dc[6] | dc[7]);
+    if ((g & 7u) == 0 && __all_sync(0xffffffffu, r.done)) break;  // decided up to g - 1: nothing left to observe
+  }
+  {
+    const uint32_t all = group8_or(d_prev);
+    r.observe_flat((all & (0x11111111u << mine)) != 0, gens, stable_interval);
+  }
+  append_hit(valid && r.hit && sub < P, id, r.first_false, r.recovered, hits, cap, n_hits);
 }
 
 // Per-pattern 64-bit fold used as a size-independent checksum (build-defined):
@@ -313,6 +463,8 @@ static void host_zoi(const uint64_t* s, uint64_t* out) {  // LifeAPI.hpp:521-536
 }
 
 // match kernels keep three tiles (state, wanted&mask, mask) in registers: cap W at 16.
+// packing 4 placements costs about 6 generations of stepping
+constexpr unsigned kEnumerateMultiFrom = 48;
 static inline int match_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
 static inline int survey_lpp(const lifeb200_ctx* ctx) { return std::max(2, effective_lpp(ctx)); }
 
@@ -381,9 +533,32 @@ int lifeb200_enumerate_collisions(lifeb200_ctx* ctx, const uint64_t* catalysts, 
   for (unsigned c = 0; c < n_catalysts; c++) host_zoi(h_cat + (size_t)c * 64, h_cz + (size_t)c * 64);
   for (unsigned g = 0; g < n_projectiles; g++) host_zoi(h_pr + (size_t)g * 64, h_pz + (size_t)g * 64);
 
+  // many generations: 4 placements per lane group in the row-class layout (enumerate_kernel_x), unless the
+  // caller pinned the lane grouping or another layout.  Its target planes are packed here: every cell of
+  // wanted (= catalyst) and mask (= its ZOI) replicated into the four pattern bits of register (column, k).
+  const bool multi = ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kEnumerateMultiFrom));
+  std::vector<uint32_t> packed;
+  if (multi) {
+    packed.resize((size_t)n_catalysts * 64 * 8 * 2);
+    uint32_t* pk_w = packed.data();
+    uint32_t* pk_m = pk_w + (size_t)n_catalysts * 64 * 8;
+    for (size_t ci = 0; ci < (size_t)n_catalysts * 64; ci++)
+      for (int k = 0; k < 8; k++) {
+        uint32_t w = 0, m = 0;
+        for (int j = 0; j < 8; j++) {
+          if (h_cat[ci] >> (8 * j + k) & 1) w |= 0xFu << (4 * j);
+          if (h_cz[ci] >> (8 * j + k) & 1) m |= 0xFu << (4 * j);
+        }
+        pk_w[ci * 8 + k] = w;
+        pk_m[ci * 8 + k] = m;
+      }
+  }
+
   uint64_t* d_tab = nullptr;
+  uint32_t* d_packed = nullptr;
   lifeb200_hit* d_hits = nullptr;
-  LIFEB200_CUDA(cudaMalloc(&d_tab, words * 8));
+  LIFEB200_CUDA(cudaMalloc(&d_tab, words * 8 + packed.size() * 4));
+  d_packed = reinterpret_cast<uint32_t*>(d_tab + words);
   cudaError_t e = cap ? cudaMalloc(&d_hits, cap * sizeof(lifeb200_hit)) : cudaSuccess;
   if (e != cudaSuccess) { cudaFree(d_tab); return cuda_fail(e, "cudaMalloc hits", __FILE__, __LINE__); }
   int rc = LIFEB200_OK;
@@ -394,10 +569,19 @@ int lifeb200_enumerate_collisions(lifeb200_ctx* ctx, const uint64_t* catalysts, 
     const uint64_t* d_cz = d_cat + (size_t)n_catalysts * 64;
     const uint64_t* d_pr = d_cz + (size_t)n_catalysts * 64;
     const uint64_t* d_pz = d_pr + (size_t)n_projectiles * 64;
-    int lpp = match_lpp(ctx);
-    LIFEB200_DISPATCH_LPP(lpp, (enumerate_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
-                                   d_cat, d_cz, d_pr, d_pz, n_projectiles, id_begin, id_end, gens, stable_interval, d_hits,
-                                   cap, ctx->d_counters + 0, ctx->d_counters + 1)));
+    if (multi) {
+      LIFEB200_CUDA(cudaMemcpyAsync(d_packed, packed.data(), packed.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+      const uint64_t groups = (id_end - (id_begin & ~3ull) + 3) / 4;
+      LIFEB200_CUDA(cudaFuncSetAttribute(enumerate_kernel_x, cudaFuncAttributeMaxDynamicSharedMemorySize, kEnumXSmem));
+      enumerate_kernel_x<<<(unsigned)((groups * 8 + 127) / 128), 128, kEnumXSmem, ctx->stream>>>(
+          d_cz, d_pr, d_pz, d_packed, d_packed + (size_t)n_catalysts * 64 * 8, n_projectiles, id_begin, id_end, gens,
+          stable_interval, d_hits, cap, ctx->d_counters + 0, ctx->d_counters + 1);
+    } else {
+      int lpp = match_lpp(ctx);
+      LIFEB200_DISPATCH_LPP(lpp, (enumerate_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
+                                     d_cat, d_cz, d_pr, d_pz, n_projectiles, id_begin, id_end, gens, stable_interval, d_hits,
+                                     cap, ctx->d_counters + 0, ctx->d_counters + 1)));
+    }
     LIFEB200_LAUNCHED(ctx);
     LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 4 * sizeof(unsigned long long),
                                   cudaMemcpyDeviceToHost, ctx->stream));

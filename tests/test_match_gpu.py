@@ -93,18 +93,37 @@ def test_enumeration_vs_reference_golden(engine):
 
 
 def test_enumeration_vs_oracle_other_catalysts(engine, port):
+    """Ragged id ranges (neither end a multiple of the 4-placement group), every kernel: lanes per pattern
+    pinned -> enumerate_kernel; default with >= 48 gens or layout 8 -> enumerate_kernel_x (4 placements per
+    lane group); layout 2 -> enumerate_kernel again."""
     c = golden("collisions.npz")
     cats = c["catalysts"]
     lo, hi = 4 * 32 * 4096 + 7, 4 * 32 * 4096 + 3 * 4096 + 11  # beehive, ragged range over 3+ glider variants
-    for lpp in (4, 16):
+    want = {}
+    for gens, interval in ((100, 5), (20, 3)):
+        want[gens] = port.enumerate(cats, c["gliders"], lo, hi, gens, interval, 1 << 14)
+    for lpp, layout, gens, interval in ((4, 0, 100, 5), (16, 0, 100, 5), (0, 0, 100, 5), (0, 8, 100, 5), (0, 2, 100, 5),
+                                        (0, 8, 20, 3), (0, 0, 20, 3)):
         engine.set_lanes_per_pattern(lpp)
+        engine.set_step_layout(layout)
         try:
-            hits, skipped = engine.enumerate_collisions(cats, c["gliders"], lo, hi, 100, 5, cap=1 << 14)
+            hits, skipped = engine.enumerate_collisions(cats, c["gliders"], lo, hi, gens, interval, cap=1 << 14)
         finally:
             engine.set_lanes_per_pattern(0)
-        ids, ff, rec, sk = port.enumerate(cats, c["gliders"], lo, hi, 100, 5, 1 << 14)
-        assert skipped == sk
+            engine.set_step_layout(0)
+        ids, ff, rec, sk = want[gens]
+        assert skipped == sk, (lpp, layout, gens)
         assert (hits["id"] == ids).all() and (hits["g_first_false"] == ff).all() and (hits["g_recovered"] == rec).all()
+    # tiny ranges inside one group, across a group edge, across a catalyst edge, and the last ids of the space
+    total = len(cats) * 32 * 4096
+    for a, b in ((5, 6), (6, 9), (32 * 4096 - 2, 32 * 4096 + 3), (total - 5, total + 100), (total, total + 4)):
+        engine.set_step_layout(8)
+        try:
+            hits, skipped = engine.enumerate_collisions(cats, c["gliders"], a, b, 60, 4, cap=64)
+        finally:
+            engine.set_step_layout(0)
+        ids, ff, rec, sk = port.enumerate(cats, c["gliders"], a, min(b, total), 60, 4, 64)
+        assert skipped == sk and (hits["id"] == ids).all() and (hits["g_first_false"] == ff).all()
 
 
 def test_soup_survey_vs_oracle(engine, port):
