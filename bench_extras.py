@@ -140,14 +140,16 @@ def config4_enumeration(eng, p_int):
 def config5_survey(eng, p_int):
     """Soups generated on device, 4096 gens, activity test + hit compaction (1/16 of the 16 Mi-soup config per call)."""
     n, gens = 1 << 20, 4096
-    t0 = time.perf_counter()
-    hits, pop_sum, hash_xor = eng.soup_survey(0, n, SEED, 0, gens, n)
-    dt = time.perf_counter() - t0
+    dt = float("inf")
+    for _ in range(2):  # the first call also loads the kernel image; report the faster of two, like config 4
+        t0 = time.perf_counter()
+        hits, pop_sum, hash_xor = eng.soup_survey(0, n, SEED, 0, gens, n)
+        dt = min(dt, time.perf_counter() - t0)
     cells = n * 4096.0 * gens
     return {"workload": f"config5 (1/16 scale): {n} on-device soups x {gens} gens, active iff state(G) != state(G-2)", "s": dt,
             "value": cells / dt / 1e9, "unit": "Gcell/s", "active": int(len(hits)), "pop_sum": int(pop_sum),
             "hash_xor": f"{int(hash_xor):016x}", "int_pipe_frac_executed": cells * (7.75 / 32.0) / dt / p_int,
-            "timing": "wall clock around the host-facing call, hits downloaded and sorted"}
+            "timing": "wall clock around the host-facing call, hits downloaded and sorted; faster of two calls"}
 
 
 def stable_propagate(eng, p_int):
