@@ -200,6 +200,20 @@ def test_config2_full_size_properties(engine, port):
     assert active == set(int(h) for h in hits["id"] if int(h) % 1024 == 0)
 
 
+def test_config2_full_size_every_final_state_vs_reference(engine, port):
+    """BASELINE config 2 at FULL size, SURVEY 8d's check as stated: ALL 1 Mi final states after 1024
+    generations equal the CPU's bit for bit.  The CPU side is the unmodified reference's Step(n)
+    (oracle/_ref) spread over every host thread, else the C port; about 10 s on the GPU box's 16 threads."""
+    from oracle.loader import Ref
+    cpu = Ref.load() or port
+    n, gens = 1 << 20, 1024
+    soups = port.soup(0, n, SEED, 0)
+    got = engine.step_batch_host(soups, gens)
+    want = cpu.step_batch(soups, gens, 0)
+    bad = np.flatnonzero((got != want).any(axis=1))
+    assert bad.size == 0, f"{bad.size} of {n} final states differ, first id {bad[:4]}"
+
+
 def test_translation_equivariance(engine, port):
     """Size-independent property: Step commutes with Moved (torus symmetry)."""
     soups = port.soup(900, 64, SEED)
