@@ -156,6 +156,15 @@ def build(code, kp, kl, kr, free=0, shape=False):
                     cnf.add(lut[i] if (lutv >> i) & 1 else -lut[i])
 
         for tag, kinds in (("l", kl), ("r", kr)):
+            if "--gshape" in sys.argv and kinds.count("L") == 4:
+                # the same topology with fewer pins: g1 = L(C0, x, y); g2 = L(C1, z, g1); g0 = L(C0, u, v) with a free
+                # LUT; out = L(w, g2, g0), w = the cell or an add gate of the tail
+                ga, gb, gc, gd = [f"{tag}{i}" for i, k in enumerate(kinds) if k == "L"]
+                force(ga, ["C0", None, None])
+                force(gb, ["C1", None, ga])
+                force(gc, ["C0", None, None])
+                force(gd, [None, gb, gc])
+                continue
             if kinds == "LLLL" and not (tag == "r" and "--shape-left" in sys.argv):
                 force(f"{tag}0", ["C0", None, None])
                 force(f"{tag}1", ["C1", None, f"{tag}0"])
@@ -176,13 +185,13 @@ def main():
         args.remove(sys.argv[sys.argv.index("--free") + 1])
     code = int(args[0])
     kp, kl, kr = [("" if a == "-" else a) for a in args[1:4]]
-    cnf, gates = build(code, kp, kl, kr, free, "--shape" in sys.argv or "--shape-left" in sys.argv)
+    cnf, gates = build(code, kp, kl, kr, free, "--shape" in sys.argv or "--shape-left" in sys.argv or "--gshape" in sys.argv)
     t0 = time.time()
     status, model = solve(cnf, timeout)
     dt = time.time() - t0
     nl = sum(k.count("L") for k in (kp, kl, kr))
     print(f"free {free} " if free else "", end="")
-    print("shape " if "--shape" in sys.argv else "shape-left " if "--shape-left" in sys.argv else "", end="")
+    print("gshape " if "--gshape" in sys.argv else "shape " if "--shape" in sys.argv else "shape-left " if "--shape-left" in sys.argv else "", end="")
     print(f"code {code} pair {kp or '-'} left {kl} right {kr} ({nl} LOP3 per column pair): vars {cnf.n} clauses "
           f"{len(cnf.clauses)} -> {status} in {dt:.1f}s", flush=True)
     if model:
