@@ -263,6 +263,80 @@ def locate_rows(eng, p_int):
             eng.free(p)
 
 
+def next_rows(eng, p_int):
+    """SURVEY 8f ranks 1-3 on resident batches: LifeWeld::Step (64 generations in registers), GetHash (XXH3-64
+    of every state) and InteractionCountsAndNext (four planes per pattern)."""
+    out = {}
+    ref = _cpu_ref()
+    n, gens = 1 << 17, 64
+    d = eng.malloc(n * 2048)
+    try:
+        eng.soup_dev(d, 0, 4 * n, SEED, 0)  # record = (state, frozen2, frozen1, frozen0), 4 x 512 B
+        recs = np.empty((n, 4, 64), dtype=np.uint64)
+        eng.d2h(recs, d)
+        eng.sync()
+        recs[:, 1] &= recs[:, 2] & recs[:, 3]   # frozen counts: sparse planes (1/8, 1/4 and 1/2 density)
+        recs[:, 2] &= recs[:, 3]
+        eng.h2d(d, recs)
+        eng.sync()
+        ms = _time(eng, lambda: eng._check(eng.lib.lifeb200_weld_step_batch_dev(eng._h, d, n, gens)))
+        out["weld_step"] = {"workload": f"LifeWeld::Step x {gens} generations on {n} records (2048 B each), in place", "ms": ms,
+                            "value": n * 4096.0 * gens / (ms * 1e-3) / 1e9, "unit": "Gcell/s"}
+        if ref is not None:
+            m = 1 << 11
+            t0 = time.perf_counter()
+            ref.weld_step(recs[:m], gens)
+            dt = time.perf_counter() - t0
+            out["weld_step"]["cpu_baseline"] = {"value": m * 4096.0 * gens / dt / 1e9, "unit": "Gcell/s", "cores": 1,
+                                                "kind": "reference", "sample": f"{m} records x {gens} gens, {dt:.2f} s, 1 thread"}
+    finally:
+        eng.free(d)
+    n = 1 << 20
+    d_s, d_h = eng.malloc(n * 512), eng.malloc(n * 8)
+    try:
+        eng.soup_dev(d_s, 0, n, SEED, 0)
+        ms = _time(eng, lambda: eng.hash_batch_dev(d_s, d_h, n))
+        out["get_hash"] = {"workload": f"GetHash (XXH3-64 of the 512-byte state) over {n} resident soups", "ms": ms,
+                           "states_per_s": n / (ms * 1e-3), "hbm_gbs": n * 520 / (ms * 1e-3) / 1e9}
+        if ref is not None:
+            m = 1 << 14
+            host = np.empty((m, 64), dtype=np.uint64)
+            eng.d2h(host, d_s)
+            got = np.empty(m, dtype=np.uint64)
+            eng.d2h(got, d_h)
+            eng.sync()
+            t0 = time.perf_counter()
+            want = [ref.hash(host[i]) for i in range(m)]
+            dt = time.perf_counter() - t0
+            out["get_hash"]["cpu_baseline"] = {"states_per_s": m / dt, "cores": 1, "kind": "reference",
+                                               "sample": f"{m} states, {dt:.2f} s, 1 thread, one ctypes call per state",
+                                               "equal_on_sample": bool((np.array(want, dtype=np.uint64) == got).all())}
+    finally:
+        eng.free(d_s)
+        eng.free(d_h)
+    n = 1 << 18
+    d_s, d_p = eng.malloc(n * 512), eng.malloc(n * 2048)
+    try:
+        eng.soup_dev(d_s, 0, n, SEED, 0)
+        ms = _time(eng, lambda: eng._check(eng.lib.lifeb200_interaction_counts_dev(eng._h, d_s, d_p, n)))
+        out["interaction_counts"] = {"workload": f"InteractionCountsAndNext over {n} resident soups (4 planes out)", "ms": ms,
+                                     "states_per_s": n / (ms * 1e-3), "hbm_gbs": n * 2560 / (ms * 1e-3) / 1e9}
+        if ref is not None:
+            m = 1 << 12
+            host = np.empty((m, 64), dtype=np.uint64)
+            eng.d2h(host, d_s)
+            eng.sync()
+            t0 = time.perf_counter()
+            ref.interaction_counts(host)
+            dt = time.perf_counter() - t0
+            out["interaction_counts"]["cpu_baseline"] = {"states_per_s": m / dt, "cores": 1, "kind": "reference",
+                                                         "sample": f"{m} states, {dt:.2f} s, 1 thread"}
+    finally:
+        eng.free(d_s)
+        eng.free(d_p)
+    return out
+
+
 def _d2d(eng, dst, src, nbytes):
     # device-to-device copy through the step entry point's gens == 0 path (a plain cudaMemcpyAsync D2D)
     return eng.lib.lifeb200_step_batch_dev(eng._h, src, dst, nbytes // 512, 0)
@@ -271,7 +345,7 @@ def _d2d(eng, dst, src, nbytes):
 def run_extras(eng, p_int):
     out = {}
     for name, fn in (("config3", config3_unknown_step), ("config4", config4_enumeration), ("config5", config5_survey),
-                     ("stable_propagate", stable_propagate), ("locate", locate_rows)):
+                     ("stable_propagate", stable_propagate), ("next_rows", next_rows), ("locate", locate_rows)):
         try:
             out[name] = fn(eng, p_int)
         except Exception as e:  # noqa: BLE001  (a side measurement must not kill the headline)

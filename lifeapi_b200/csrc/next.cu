@@ -12,7 +12,6 @@ namespace lifeb200 {
 
 constexpr int kBlockN = 256;
 static inline unsigned grid_n(size_t n, int lpp) { return (unsigned)((n * (size_t)lpp + kBlockN - 1) / kBlockN); }
-
 // ---- LifeWeld::Step: 3x3 count (bit3 dropped, as the reference does) + frozen count, then the rule ----
 template <int LPP>
 __global__ void __launch_bounds__(kBlockN, 1) weld_step_kernel(uint64_t* __restrict__ records, size_t n, unsigned gens) {
@@ -91,57 +90,92 @@ __global__ void __launch_bounds__(kBlockN) interaction_kernel(const uint64_t* __
   o1.store(o, sub); o2.store(o + kN, sub); om.store(o + 2 * kN, sub); nx.store(o + 3 * kN, sub);
 }
 
-// ---- XXH3_64bits(state, 512): 8 stripes of 64 bytes; 8 lanes per pattern, one stripe per lane ----
+// ---- XXH3_64bits(state, 512): 8 stripes of 64 bytes.  A warp hashes 4 patterns (2 KiB) at a time: every
+// load is one contiguous 512-byte request, lane L holding bytes [16 L, 16 L + 16) of each pattern = the two
+// accumulator lanes i0 = 2 (L & 3), i0 + 1 of stripe L >> 2.  accumulate_512 only ADDS into the accumulators
+// and a 512-byte input has no scramble round, so the stripes commute: partial sums are reduced across the
+// eight stripe lanes, four patterns at once (each butterfly step keeps half of the patterns and sends the
+// other half: 4 + 2 + 2 64-bit shuffles instead of 3 x 8).
 __constant__ uint64_t c_stripe_keys[8][8] = {LIFEB200_XXH3_STRIPE_KEYS};
 __constant__ uint64_t c_merge_keys[8] = {LIFEB200_XXH3_MERGE_KEYS};
+__constant__ uint64_t c_acc_init[8] = {xxh3::kPrime32_3, xxh3::kPrime64_1, xxh3::kPrime64_2, xxh3::kPrime64_3,
+                                       xxh3::kPrime64_4, xxh3::kPrime32_2, xxh3::kPrime64_5, xxh3::kPrime32_1};
 
 __device__ __forceinline__ uint64_t fold128(uint64_t a, uint64_t b) { return (a * b) ^ __umul64hi(a, b); }
+__device__ __forceinline__ uint64_t shfl_xor64(uint64_t v, int o) { return __shfl_xor_sync(0xffffffffu, v, o); }
 
 __global__ void __launch_bounds__(kBlockN) hash_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ hashes,
                                                        size_t n) {
-  constexpr int LPP = 8;
-  const size_t p = ((size_t)blockIdx.x * kBlockN + threadIdx.x) / LPP;
-  const int sub = threadIdx.x & (LPP - 1);  // = stripe index
-  const bool valid = p < n;
-  Tile<LPP> t;
-  if (valid) t.load(in + p * kN, sub);
-  else {
+  const size_t warps = ((size_t)gridDim.x * kBlockN) >> 5, groups = (n + 3) / 4;
+  size_t g = ((size_t)blockIdx.x * kBlockN + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31, stripe = lane >> 2, i0 = 2 * (lane & 3);
+  if (g >= groups) return;  // warp-uniform
+  const uint64_t key0 = c_stripe_keys[stripe][i0], key1 = c_stripe_keys[stripe][i0 + 1];
+  const uint64_t init0 = c_acc_init[i0], init1 = c_acc_init[i0 + 1], mk0 = c_merge_keys[i0], mk1 = c_merge_keys[i0 + 1];
+  const bool hi4 = lane & 16, hi3 = lane & 8;
+  auto fetch = [&](size_t grp, uint4 (&v)[4]) {
 #pragma unroll
-    for (int w = 0; w < 8; w++) t.lo[w] = t.hi[w] = 0;
-  }
-  // accumulate_512 of this lane's stripe; sums commute, so stripes are added across lanes afterwards
-  uint64_t acc[8];
+    for (int k = 0; k < 4; k++) {
+      v[k] = make_uint4(0, 0, 0, 0);
+      if (grp * 4 + k < n) v[k] = __ldg(reinterpret_cast<const uint4*>(in + (grp * 4 + k) * kN) + lane);
+    }
+  };
+  uint4 v[4], nv[4];
+  fetch(g, v);
+  // a persistent warp walks groups g, g + warps, ..: the next group's four requests are in flight while this
+  // one is reduced (one short-lived CTA per 32 patterns was bound by CTA launch rate, not by HBM)
+  for (; g < groups; g += warps) {
+    const bool more = g + warps < groups;
+    if (more) fetch(g + warps, nv);
+    uint64_t a0[4], a1[4];  // this lane's share of acc[i0], acc[i0 + 1] of patterns 4 g .. 4 g + 3
 #pragma unroll
-  for (int i = 0; i < 8; i++) acc[i] = 0;
+    for (int k = 0; k < 4; k++) {
+      const uint64_t d0 = ((uint64_t)v[k].y << 32) | v[k].x, d1 = ((uint64_t)v[k].w << 32) | v[k].z;
+      const uint64_t k0 = d0 ^ key0, k1 = d1 ^ key1;
+      a0[k] = (k0 & 0xffffffffULL) * (k0 >> 32) + d1;  // acc[i] += lo * hi;  acc[i ^ 1] += data
+      a1[k] = (k1 & 0xffffffffULL) * (k1 >> 32) + d0;
+    }
+    // sum over the 8 stripes (lane bits 2..4).  Bit 4 splits patterns {0,1} | {2,3}, bit 3 splits the pair.
+    uint64_t b0[2], b1[2];
 #pragma unroll
-  for (int i = 0; i < 8; i++) {
-    const uint64_t d = ((uint64_t)t.hi[i] << 32) | t.lo[i];
-    const uint64_t k = d ^ c_stripe_keys[sub][i];
-    acc[i ^ 1] += d;
-    acc[i] += (k & 0xffffffffULL) * (k >> 32);
-  }
-#pragma unroll
-  for (int i = 0; i < 8; i++) {
-#pragma unroll
-    for (int o = 4; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o, 8);
-  }
-  if (valid && sub == 0) {
-    const uint64_t init[8] = {xxh3::kPrime32_3, xxh3::kPrime64_1, xxh3::kPrime64_2, xxh3::kPrime64_3,
-                              xxh3::kPrime64_4, xxh3::kPrime32_2, xxh3::kPrime64_5, xxh3::kPrime32_1};
-    uint64_t r = 512ULL * xxh3::kPrime64_1;
-#pragma unroll
-    for (int k = 0; k < 4; k++)
-      r += fold128((acc[2 * k] + init[2 * k]) ^ c_merge_keys[2 * k], (acc[2 * k + 1] + init[2 * k + 1]) ^ c_merge_keys[2 * k + 1]);
+    for (int j = 0; j < 2; j++) {
+      const uint64_t keep0 = hi4 ? a0[2 + j] : a0[j], send0 = hi4 ? a0[j] : a0[2 + j];
+      const uint64_t keep1 = hi4 ? a1[2 + j] : a1[j], send1 = hi4 ? a1[j] : a1[2 + j];
+      b0[j] = keep0 + shfl_xor64(send0, 16);
+      b1[j] = keep1 + shfl_xor64(send1, 16);
+    }
+    uint64_t c0 = (hi3 ? b0[1] : b0[0]) + shfl_xor64(hi3 ? b0[0] : b0[1], 8);
+    uint64_t c1 = (hi3 ? b1[1] : b1[0]) + shfl_xor64(hi3 ? b1[0] : b1[1], 8);
+    c0 += shfl_xor64(c0, 4);
+    c1 += shfl_xor64(c1, 4);
+    // lanes with (bit 4, bit 3) = (h, l) now hold the full acc[i0], acc[i0 + 1] of pattern 2 h + l: mergeAccs
+    uint64_t r = fold128((c0 + init0) ^ mk0, (c1 + init1) ^ mk1);
+    r += shfl_xor64(r, 1);
+    r += shfl_xor64(r, 2);
+    r += 512ULL * xxh3::kPrime64_1;
     r ^= r >> 37;
     r *= xxh3::kPrimeMx1;
     r ^= r >> 32;
-    hashes[p] = r;
+    const size_t p = g * 4 + (hi4 ? 2 : 0) + (hi3 ? 1 : 0);
+    if ((lane & 7) == 0 && p < n) hashes[p] = r;
+    if (more) {
+#pragma unroll
+      for (int k = 0; k < 4; k++) v[k] = nv[k];
+    }
   }
 }
 
 }  // namespace lifeb200
 
 using namespace lifeb200;
+
+// persistent warps for hash_kernel: exactly as many CTAs as are resident at once (one wave, no tail)
+static unsigned grid_hash(const lifeb200_ctx* ctx, size_t n) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hash_kernel, kBlockN, 0) != cudaSuccess || per_sm < 1) per_sm = 2;
+  const unsigned resident = (unsigned)(ctx->sm_count > 0 ? ctx->sm_count : 148) * (unsigned)per_sm;
+  return std::min(grid_n((n + 3) / 4, 32), resident);
+}
 
 extern "C" {
 
@@ -169,7 +203,7 @@ int lifeb200_hash_batch_dev(lifeb200_ctx* ctx, const uint64_t* patterns, uint64_
   LIFEB200_CHECK_CTX(ctx);
   if (n == 0) return LIFEB200_OK;
   if (!patterns || !hashes || !aligned16(patterns)) return set_error(LIFEB200_E_ARG, "null or misaligned pointer");
-  hash_kernel<<<grid_n(n, 8), kBlockN, 0, ctx->stream>>>(patterns, hashes, n);
+  hash_kernel<<<grid_hash(ctx, n), kBlockN, 0, ctx->stream>>>(patterns, hashes, n);
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }
@@ -191,7 +225,7 @@ int lifeb200_hash_batch_host(lifeb200_ctx* ctx, const uint64_t* patterns, uint64
     uint64_t* d = static_cast<uint64_t*>(sl.dbuf);
     uint64_t* dh = static_cast<uint64_t*>(sl.dbuf2);
     LIFEB200_CUDA(cudaMemcpyAsync(d, patterns + off * kN, cnt * LIFEB200_PATTERN_BYTES, cudaMemcpyHostToDevice, sl.stream));
-    hash_kernel<<<grid_n(cnt, 8), kBlockN, 0, sl.stream>>>(d, dh, cnt);
+    hash_kernel<<<grid_hash(ctx, cnt), kBlockN, 0, sl.stream>>>(d, dh, cnt);
     LIFEB200_LAUNCHED(ctx);
     LIFEB200_CUDA(cudaMemcpyAsync(hashes + off, dh, cnt * sizeof(uint64_t), cudaMemcpyDeviceToHost, sl.stream));
   }
