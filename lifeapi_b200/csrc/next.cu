@@ -78,7 +78,10 @@ __device__ __forceinline__ void interaction_planes(const Tile<LPP>& s, int sub, 
   }
 }
 
-// lane-group form (an explicit lifeb200_set_lanes_per_pattern): a lane owns kN / LPP consecutive words
+// A lane owns kN / LPP consecutive words.  Default LPP = 32 (a warp per pattern, lane L owns words 2 L, 2 L + 1):
+// the load and each of the four plane stores is ONE contiguous 512-byte request per warp.  With 8 lanes per
+// pattern a store instruction writes 16-byte pieces 64 bytes apart, four times the sectors per request:
+// 4.9 TB/s against 6.7 TB/s on 1 Mi soups (profiles/r01o_interaction.txt; 512 B in + 2 KiB out per pattern).
 template <int LPP>
 __global__ void __launch_bounds__(kBlockN) interaction_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
                                                               size_t n) {
@@ -96,33 +99,6 @@ __global__ void __launch_bounds__(kBlockN) interaction_kernel(const uint64_t* __
   if (!valid) return;
   uint64_t* o = out + p * 4 * kN;
   o1.store(o, sub); o2.store(o + kN, sub); om.store(o + 2 * kN, sub); nx.store(o + 3 * kN, sub);
-}
-
-// default form: a warp per pattern, lane L owns words 2 L, 2 L + 1, so the load and each of the four plane
-// stores is ONE contiguous 512-byte request (the lane-group form writes 16-byte pieces 64 bytes apart: four
-// times the sectors per instruction).  The pass is HBM-bound (512 B in, 2 KiB out per pattern, about 25 issue
-// cycles of arithmetic): warps are persistent and keep the next pattern's load in flight, as in hash_kernel.
-__global__ void __launch_bounds__(kBlockN) interaction_kernel_w(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
-                                                                size_t n) {
-  const size_t warps = ((size_t)gridDim.x * kBlockN) >> 5;
-  size_t p = ((size_t)blockIdx.x * kBlockN + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (p >= n) return;  // warp-uniform
-  uint4 v = __ldg(reinterpret_cast<const uint4*>(in + p * kN) + lane);
-  for (; p < n; p += warps) {
-    const bool more = p + warps < n;
-    uint4 nv = v;
-    if (more) nv = __ldg(reinterpret_cast<const uint4*>(in + (p + warps) * kN) + lane);
-    Tile<32> s, o1, o2, om, nx;
-    s.lo[0] = v.x; s.hi[0] = v.y; s.lo[1] = v.z; s.hi[1] = v.w;
-    interaction_planes<32>(s, lane, o1, o2, om, nx);
-    uint4* o = reinterpret_cast<uint4*>(out + p * 4 * kN) + lane;
-    __stcs(o, make_uint4(o1.lo[0], o1.hi[0], o1.lo[1], o1.hi[1]));
-    __stcs(o + 32, make_uint4(o2.lo[0], o2.hi[0], o2.lo[1], o2.hi[1]));
-    __stcs(o + 64, make_uint4(om.lo[0], om.hi[0], om.lo[1], om.hi[1]));
-    __stcs(o + 96, make_uint4(nx.lo[0], nx.hi[0], nx.lo[1], nx.hi[1]));
-    v = nv;
-  }
 }
 
 // ---- XXH3_64bits(state, 512): 8 stripes of 64 bytes.  A warp hashes 4 patterns (2 KiB) at a time: every
@@ -204,16 +180,13 @@ __global__ void __launch_bounds__(kBlockN) hash_kernel(const uint64_t* __restric
 
 using namespace lifeb200;
 
-// persistent warps (hash_kernel, interaction_kernel_w): exactly as many CTAs as are resident at once (one
-// wave, no tail); `warp_items` = how many warps' worth of work there is
-template <typename K>
-static unsigned grid_persistent(const lifeb200_ctx* ctx, K kernel, size_t warp_items) {
+// persistent warps for hash_kernel: exactly as many CTAs as are resident at once (one wave, no tail)
+static unsigned grid_hash(const lifeb200_ctx* ctx, size_t n) {
   int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlockN, 0) != cudaSuccess || per_sm < 1) per_sm = 2;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hash_kernel, kBlockN, 0) != cudaSuccess || per_sm < 1) per_sm = 2;
   const unsigned resident = (unsigned)(ctx->sm_count > 0 ? ctx->sm_count : 148) * (unsigned)per_sm;
-  return std::min(grid_n(warp_items, 32), resident);
+  return std::min(grid_n((n + 3) / 4, 32), resident);
 }
-static unsigned grid_hash(const lifeb200_ctx* ctx, size_t n) { return grid_persistent(ctx, hash_kernel, (n + 3) / 4); }
 
 extern "C" {
 
@@ -231,12 +204,8 @@ int lifeb200_interaction_counts_dev(lifeb200_ctx* ctx, const uint64_t* in, uint6
   LIFEB200_CHECK_CTX(ctx);
   if (n == 0) return LIFEB200_OK;
   if (!in || !planes || !aligned16(in) || !aligned16(planes)) return set_error(LIFEB200_E_ARG, "null or misaligned pointer");
-  if (ctx->lpp == 0) {
-    interaction_kernel_w<<<grid_persistent(ctx, interaction_kernel_w, n), kBlockN, 0, ctx->stream>>>(in, planes, n);
-  } else {
-    int lpp = std::max(8, ctx->lpp);
-    LIFEB200_DISPATCH_LPP(lpp, (interaction_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, ctx->stream>>>(in, planes, n)));
-  }
+  int lpp = ctx->lpp ? std::max(8, ctx->lpp) : 32;
+  LIFEB200_DISPATCH_LPP(lpp, (interaction_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, ctx->stream>>>(in, planes, n)));
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }
