@@ -156,12 +156,14 @@ __device__ __forceinline__ unsigned synchronise(Stable& s) {
 }
 
 // LifeStable.hpp:558-615
-__device__ __forceinline__ unsigned update_options(Stable& s, int lane) {
+// (on2, on1, on0) = the low three planes of NeighbourCount(state); the pass does not write `state`, so
+// PropagateStep hands the same planes on to SignalNeighbours
+// and returns (f3..f0) = NeighbourCount(known off), from which it derives NeighbourCount(state | unknown)
+__device__ __forceinline__ unsigned update_options(Stable& s, int lane, const T32& on2, const T32& on1, const T32& on0,
+                                                   T32& f3, T32& f2, T32& f1, T32& f0) {
   T32 known_off;
 #pragma unroll
   for (int k = 0; k < kRegs; k++) reg(known_off, k) = ~reg(s.p[S_UNKNOWN], k) & ~reg(s.p[S_STATE], k);
-  T32 on3, on2, on1, on0, f3, f2, f1, f0;
-  s.p[S_STATE].neighbour_count(lane, on3, on2, on1, on0);
   known_off.neighbour_count(lane, f3, f2, f1, f0);
   uint32_t has_abort = 0, changes = 0;
 #pragma unroll
@@ -178,15 +180,15 @@ __device__ __forceinline__ unsigned update_options(Stable& s, int lane) {
   }
   return (warp_any(has_abort) ? 0u : kConsistent) | (warp_any(changes) ? kChanged : 0u);
 }
+__device__ __forceinline__ unsigned update_options(Stable& s, int lane) {
+  T32 on3, on2, on1, on0, f3, f2, f1, f0;
+  s.p[S_STATE].neighbour_count(lane, on3, on2, on1, on0);
+  return update_options(s, lane, on2, on1, on0, f3, f2, f1, f0);
+}
 
-// LifeStable.hpp:617-675
-__device__ __forceinline__ unsigned signal_neighbours(Stable& s, int lane) {
-  T32 maxp;
-#pragma unroll
-  for (int k = 0; k < kRegs; k++) reg(maxp, k) = reg(s.p[S_STATE], k) | reg(s.p[S_UNKNOWN], k);
-  T32 s3, s2, s1, s0, m3, m2, m1, m0;
-  s.p[S_STATE].neighbour_count(lane, s3, s2, s1, s0);
-  maxp.neighbour_count(lane, m3, m2, m1, m0);
+// LifeStable.hpp:617-675; (s2, s1, s0) = low planes of NeighbourCount(state), (m3..m0) = NeighbourCount(state | unknown)
+__device__ __forceinline__ unsigned signal_neighbours(Stable& s, int lane, const T32& s2, const T32& s1, const T32& s0,
+                                                      const T32& m3, const T32& m2, const T32& m1, const T32& m0) {
   T32 sig_off, sig_on, cen_off, cen_on;
 #pragma unroll
   for (int k = 0; k < kRegs; k++) {
@@ -209,6 +211,15 @@ __device__ __forceinline__ unsigned signal_neighbours(Stable& s, int lane) {
   set_off(s, off_zoi);
   set_on(s, on_zoi);
   return kConsistent | (warp_any(changes) ? kChanged : 0u);
+}
+__device__ __forceinline__ unsigned signal_neighbours(Stable& s, int lane) {
+  T32 maxp;
+#pragma unroll
+  for (int k = 0; k < kRegs; k++) reg(maxp, k) = reg(s.p[S_STATE], k) | reg(s.p[S_UNKNOWN], k);
+  T32 s3, s2, s1, s0, m3, m2, m1, m0;
+  s.p[S_STATE].neighbour_count(lane, s3, s2, s1, s0);
+  maxp.neighbour_count(lane, m3, m2, m1, m0);
+  return signal_neighbours(s, lane, s2, s1, s0, m3, m2, m1, m0);
 }
 
 // LifeStable.hpp:677-693
@@ -242,9 +253,22 @@ __device__ __forceinline__ unsigned propagate_simple(Stable& s, int lane) {
 __device__ __forceinline__ unsigned propagate_step(Stable& s, int lane) {
   const unsigned k = synchronise(s);
   if (!(k & kConsistent)) return 0;
-  const unsigned o = update_options(s, lane);
+  // UpdateOptions writes neither `state` nor `unknown`, so of the four NeighbourCounts the two passes take, two
+  // are needed: NeighbourCount(state) serves both, and state | unknown is the complement of known-off, whose
+  // 3x3 count f (0..9, exact) gives NeighbourCount(state | unknown) = 9 - f plane by plane.
+  T32 on3, on2, on1, on0, f3, f2, f1, f0;
+  s.p[S_STATE].neighbour_count(lane, on3, on2, on1, on0);
+  const unsigned o = update_options(s, lane, on2, on1, on0, f3, f2, f1, f0);
   if (!(o & kConsistent)) return 0;
-  const unsigned g = signal_neighbours(s, lane);
+  T32 m3, m2, m1, m0;
+#pragma unroll
+  for (int k = 0; k < kRegs; k++) {
+    reg(m0, k) = ~reg(f0, k);                                 // 9 - f: 9..0 = 1001 1000 0111 0110 0101 0100 0011 0010 0001 0000
+    reg(m1, k) = reg(f1, k);
+    reg(m2, k) = reg(f2, k) ^ reg(f1, k);
+    reg(m3, k) = ~(reg(f3, k) | reg(f2, k) | reg(f1, k));
+  }
+  const unsigned g = signal_neighbours(s, lane, on2, on1, on0, m3, m2, m1, m0);
   if (!(g & kConsistent)) return 0;
   return kConsistent | ((k | o | g) & kChanged);
 }
