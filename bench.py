@@ -247,6 +247,11 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    # one process per GPU: keep each rank (and the pinned buffers it touches first) on its GPU's NUMA node
+    host_affinity = "all cores (single process)"
+    if distributed:
+        from lifeapi_b200 import bind_host_to_device
+        host_affinity = bind_host_to_device(local_rank)
     eng = Engine(local_rank)
     if args.lpp:
         eng.set_lanes_per_pattern(args.lpp)
@@ -336,13 +341,21 @@ def main():
         for _ in range(args.steps):
             eng.step_batch_host(h_in, gens, out=h_out)
         torch.cuda.synchronize()
-        dt = max_over_ranks(time.perf_counter() - t0)
+        dt_local = time.perf_counter() - t0
+        dt = max_over_ranks(dt_local)
+        by_rank = [dt_local]
+        if distributed:
+            t = torch.tensor([dt_local], dtype=torch.float64, device=dev)
+            ts = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(ts, t)
+            by_rank = [float(x.item()) for x in ts]
         # result check: the host path's output equals the resident path's (same checksum)
         eng.h2d(d_out, h_out)
         chk = eng.fold_dev(d_out, n, first_id)
         e2e = {"value": cells_per_step_all * args.steps / dt / 1e9, "unit": UNIT, "h2d_bytes_per_step": nbytes * world,
                "d2h_bytes_per_step": nbytes * world, "ms_per_step": dt / args.steps * 1e3,
-               "host_memory": "pinned (lifeb200_host_alloc)", "api": "lifeb200_step_batch_host",
+               "ms_per_step_by_rank": [round(x / args.steps * 1e3, 3) for x in by_rank],
+               "host_memory": "pinned (lifeb200_host_alloc)", "host_affinity": host_affinity, "api": "lifeb200_step_batch_host",
                "matches_resident_path": bool(distributed or chk == (pop_sum, hash_xor))}
         eng.host_free(h_in)
         eng.host_free(h_out)

@@ -9,7 +9,8 @@
 
 namespace lifeb200 {
 
-constexpr int kSlots = 3;  // host-path pipeline depth (H2D | kernel | D2H in flight)
+constexpr int kSlots = 3;  // host-path pipeline depth (H2D | kernel | D2H in flight).  6 slots were tried for the 8-rank
+                           // e2e case and lost (64.6 against 63.3 ms on the GPUs behind the shared PCIe uplink)
 
 struct Slot {
   cudaStream_t stream = nullptr;

@@ -20,6 +20,31 @@ def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:
     return n * rank // world, n * (rank + 1) // world
 
 
+def bind_host_to_device(device_index: int) -> str:
+    """Pin the calling process to the CPU cores next to GPU `device_index` (NVML's ideal affinity), so the
+    pinned host buffers of lifeb200_host_alloc are first touched on that GPU's NUMA node and the host
+    pipeline's copies of 8 ranks do not all cross the socket link.  One process per GPU only: a single
+    process that also runs the host-thread CPU baseline must keep every core.  Returns what was done."""
+    import os
+    if os.environ.get("LIFEB200_NO_NUMA_BIND"):
+        return "off (LIFEB200_NO_NUMA_BIND)"
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        try:
+            pr = torch.cuda.get_device_properties(device_index)
+            bus_id = f"{pr.pci_domain_id:08x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+            handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus_id.encode())
+        except Exception:
+            handle = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        pynvml.nvmlDeviceSetCpuAffinity(handle)
+        cores = sorted(os.sched_getaffinity(0))
+        return f"{len(cores)} cores ({cores[0]}..{cores[-1]})"
+    except Exception as exc:  # affinity is an optimisation, never a requirement
+        return f"unavailable ({type(exc).__name__}: {exc})"
+
+
 def merge_hits(per_rank: list[np.ndarray]) -> np.ndarray:
     """Concatenate per-rank hit records and sort by id (deterministic order for comparison)."""
     parts = [np.asarray(h, dtype=HIT_DTYPE) for h in per_rank if len(h)]
