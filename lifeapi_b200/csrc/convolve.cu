@@ -25,7 +25,14 @@ struct Plane {
   uint64_t w0, w1;  // words 2L, 2L+1 of this lane
 };
 
-__device__ __forceinline__ uint64_t rotl64(uint64_t v, int s) { return (v << (s & 63)) | (v >> ((64 - s) & 63)); }
+// 64-bit rotate as two 32-bit funnel shifts (SHF.L.W) after a half swap for s >= 32: 2 SHF + 2 SEL, where
+// (v << s) | (v >> (64 - s)) on a 64-bit value compiles to two variable 64-bit shifts and two ORs
+__device__ __forceinline__ uint64_t rotl64(uint64_t v, int s) {
+  uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
+  if (s & 32) { const uint32_t t = lo; lo = hi; hi = t; }
+  const uint32_t nlo = __funnelshift_l(hi, lo, s), nhi = __funnelshift_l(lo, hi, s);  // shift taken mod 32
+  return ((uint64_t)nhi << 32) | nlo;
+}
 __device__ __forceinline__ uint64_t shfl64(uint64_t v, int src) { return __shfl_sync(kFull, v, src & 31); }
 
 __device__ __forceinline__ Plane load_plane(const uint64_t* __restrict__ p, int lane) {
@@ -59,7 +66,29 @@ __device__ __forceinline__ Plane mirrored(const Plane& s, int lane) {
 }
 
 // acc |= OR over ON bits k of x of rotl(y, k), for this lane's two result words (x is warp-uniform)
+// Sparse columns (the usual case: the walked operand is a catalyst, a target or an 8x8 object) go bit by bit on
+// 32-bit halves: find-first-set, clear, and a rotate that is two funnel shifts because the half says whether the
+// words' halves swap -- about 14 instructions per ON cell, where the run logic on 64-bit values costs about 50 per
+// run.  Denser columns keep the doubling, which is what bounds the cost of solid blobs.
+constexpr int kBitwiseMax = 12;
 __device__ __forceinline__ void spread(uint64_t x, uint64_t y0, uint64_t y1, Plane& acc) {
+  if (__popcll(x) <= kBitwiseMax) {  // warp-uniform
+    const uint32_t y0l = (uint32_t)y0, y0h = (uint32_t)(y0 >> 32), y1l = (uint32_t)y1, y1h = (uint32_t)(y1 >> 32);
+    uint32_t a0l = 0, a0h = 0, a1l = 0, a1h = 0;
+    for (uint32_t xl = (uint32_t)x; xl; xl &= xl - 1) {  // rotl by k < 32
+      const int k = __ffs(xl) - 1;
+      a0l |= __funnelshift_l(y0h, y0l, k); a0h |= __funnelshift_l(y0l, y0h, k);
+      a1l |= __funnelshift_l(y1h, y1l, k); a1h |= __funnelshift_l(y1l, y1h, k);
+    }
+    for (uint32_t xh = (uint32_t)(x >> 32); xh; xh &= xh - 1) {  // rotl by 32 + k: halves swapped
+      const int k = __ffs(xh) - 1;
+      a0l |= __funnelshift_l(y0l, y0h, k); a0h |= __funnelshift_l(y0h, y0l, k);
+      a1l |= __funnelshift_l(y1l, y1h, k); a1h |= __funnelshift_l(y1h, y1l, k);
+    }
+    acc.w0 |= ((uint64_t)a0h << 32) | a0l;
+    acc.w1 |= ((uint64_t)a1h << 32) | a1l;
+    return;
+  }
   while (x) {
     const int k = __ffsll((long long)x) - 1;
     const uint64_t sh = x >> k;
