@@ -40,6 +40,15 @@ int ensure_slot(lifeb200_ctx* ctx, int s, size_t bytes, size_t bytes2) {
   return LIFEB200_OK;
 }
 
+int ensure_scratch(void*& buf, size_t& cap, size_t bytes) {
+  if (cap >= bytes) return LIFEB200_OK;
+  if (buf) LIFEB200_CUDA(cudaFree(buf));  // synchronises the device: earlier users of the block are done
+  buf = nullptr; cap = 0;
+  LIFEB200_CUDA(cudaMalloc(&buf, bytes));
+  cap = bytes;
+  return LIFEB200_OK;
+}
+
 }  // namespace lifeb200
 
 using namespace lifeb200;
@@ -100,6 +109,8 @@ int lifeb200_destroy(lifeb200_ctx* c) {
     if (s.dbuf) cudaFree(s.dbuf);
     if (s.dbuf2) cudaFree(s.dbuf2);
   }
+  if (c->d_hitbuf) cudaFree(c->d_hitbuf);
+  if (c->d_tabbuf) cudaFree(c->d_tabbuf);
   if (c->d_counters) cudaFree(c->d_counters);
   if (c->h_counters) cudaFreeHost(c->h_counters);
   if (c->ev_start) cudaEventDestroy(c->ev_start);

@@ -38,6 +38,13 @@ struct lifeb200_ctx {
   // small device scratch for counters: [0]=n_hits [1]=n_skipped [2]=pop_sum [3]=hash_xor
   unsigned long long* d_counters = nullptr;
   unsigned long long* h_counters = nullptr;  // pinned mirror
+  // grow-only device scratch of the host-facing enumeration / survey calls (hit records, catalyst and projectile
+  // tables): allocated on first use, reused by every later call, freed by lifeb200_destroy -- cudaMalloc / cudaFree
+  // cost milliseconds and cudaFree synchronises the device, so they stay out of the per-batch path
+  void* d_hitbuf = nullptr;
+  size_t hitbuf_cap = 0;
+  void* d_tabbuf = nullptr;
+  size_t tabbuf_cap = 0;
 };
 
 namespace lifeb200 {
@@ -45,6 +52,7 @@ namespace lifeb200 {
 int set_error(int code, const char* fmt, ...);
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 int ensure_slot(lifeb200_ctx* ctx, int slot, size_t bytes, size_t bytes2);
+int ensure_scratch(void*& buf, size_t& cap, size_t bytes);  // grow-only; the old block is released after a stream sync
 
 #define LIFEB200_CUDA(expr)                                                        \
   do {                                                                             \

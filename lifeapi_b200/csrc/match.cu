@@ -557,10 +557,14 @@ int lifeb200_enumerate_collisions(lifeb200_ctx* ctx, const uint64_t* catalysts, 
   uint64_t* d_tab = nullptr;
   uint32_t* d_packed = nullptr;
   lifeb200_hit* d_hits = nullptr;
-  LIFEB200_CUDA(cudaMalloc(&d_tab, words * 8 + packed.size() * 4));
+  // context-owned scratch (ctx.h): no allocation after the first call of a given size
+  if (int rc0 = ensure_scratch(ctx->d_tabbuf, ctx->tabbuf_cap, words * 8 + packed.size() * 4)) return rc0;
+  d_tab = static_cast<uint64_t*>(ctx->d_tabbuf);
   d_packed = reinterpret_cast<uint32_t*>(d_tab + words);
-  cudaError_t e = cap ? cudaMalloc(&d_hits, cap * sizeof(lifeb200_hit)) : cudaSuccess;
-  if (e != cudaSuccess) { cudaFree(d_tab); return cuda_fail(e, "cudaMalloc hits", __FILE__, __LINE__); }
+  if (cap) {
+    if (int rc0 = ensure_scratch(ctx->d_hitbuf, ctx->hitbuf_cap, cap * sizeof(lifeb200_hit))) return rc0;
+    d_hits = static_cast<lifeb200_hit*>(ctx->d_hitbuf);
+  }
   int rc = LIFEB200_OK;
   auto body = [&]() -> int {
     LIFEB200_CUDA(cudaMemcpyAsync(d_tab, tab.data(), words * 8, cudaMemcpyHostToDevice, ctx->stream));
@@ -590,8 +594,6 @@ int lifeb200_enumerate_collisions(lifeb200_ctx* ctx, const uint64_t* catalysts, 
     return fetch_hits(ctx, d_hits, cap, hits, n_hits);
   };
   rc = body();
-  cudaFree(d_tab);
-  if (d_hits) cudaFree(d_hits);
   return rc;
 }
 
@@ -606,7 +608,10 @@ int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_
   if (n == 0) return LIFEB200_OK;
   if (!hits && cap) return set_error(LIFEB200_E_ARG, "null hits with non-zero capacity");
   lifeb200_hit* d_hits = nullptr;
-  if (cap) LIFEB200_CUDA(cudaMalloc(&d_hits, cap * sizeof(lifeb200_hit)));
+  if (cap) {
+    if (int rc0 = ensure_scratch(ctx->d_hitbuf, ctx->hitbuf_cap, cap * sizeof(lifeb200_hit))) return rc0;
+    d_hits = static_cast<lifeb200_hit*>(ctx->d_hitbuf);
+  }
   auto body = [&]() -> int {
     LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
     // many generations: 4 soups per lane group in the row-class layout (life_multi.cuh), unless the caller
@@ -630,9 +635,7 @@ int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_
     if (hash_xor) *hash_xor = ctx->h_counters[3];
     return fetch_hits(ctx, d_hits, cap, hits, n_hits);
   };
-  int rc = body();
-  if (d_hits) cudaFree(d_hits);
-  return rc;
+  return body();
 }
 
 int lifeb200_fold_dev(lifeb200_ctx* ctx, const uint64_t* patterns, size_t n, uint64_t first_id, uint64_t* pop_sum,
