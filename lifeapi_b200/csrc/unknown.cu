@@ -39,39 +39,57 @@ __device__ __forceinline__ void unknown_step_tile(Tile<LPP>& s, Tile<LPP>& u, in
 // overlapping planes is outside the generator's domain and follows the fragment text literally
 // (unknown_step_tile), so the result is the cover's on EVERY input.  The choice is per warp because
 // both paths shuffle with a full mask.
+// Lane groups are persistent: a group walks patterns p, p + stride, ... and, with 16 or 32 lanes per pattern, issues the
+// NEXT pattern's loads before it steps the current one.  One pattern per short-lived group left the HBM phase
+// exposed (config 3, 16 generations: 0.816 ms = 16 x 0.047 ms of stepping + 0.067 ms of load / store): every
+// CTA of a wave takes the same time, so co-resident CTAs load, step and store in lockstep and nothing overlaps.
 template <int LPP, bool IL>
 __global__ void __launch_bounds__(kBlockU, 1) unknown_step_kernel(const uint64_t* __restrict__ state_in,
                                                                const uint64_t* __restrict__ unknown_in,
                                                                uint64_t* __restrict__ state_out,
                                                                uint64_t* __restrict__ unknown_out, size_t n,
                                                                unsigned gens, int force_literal) {
+  constexpr bool kPrefetch = LPP >= 16;  // 2 x W more registers; 8 or 4 lanes per pattern have none to spare
   const size_t gid = (size_t)blockIdx.x * kBlockU + threadIdx.x;
-  const size_t p = gid / LPP;
+  const size_t stride = (size_t)gridDim.x * kBlockU / LPP;
+  size_t p = gid / LPP;
+  size_t pw = (gid - (threadIdx.x & 31)) / LPP;  // first pattern of this warp: the loop bound is warp-uniform
   const int sub = threadIdx.x & (LPP - 1);
-  const bool valid = p < n;
-  Tile<LPP> s, u;
-  if (valid) {
-    s.load(state_in + p * kN, sub);
-    u.load(unknown_in + p * kN, sub);
-  } else {
+  Tile<LPP> s, u, ns, nu;
+  auto fetch = [&](size_t q, Tile<LPP>& ts, Tile<LPP>& tu) {
+    if (q < n) {
+      ts.load(state_in + q * kN, sub);
+      tu.load(unknown_in + q * kN, sub);
+    } else {
 #pragma unroll
-    for (int w = 0; w < Tile<LPP>::W; w++) s.lo[w] = s.hi[w] = u.lo[w] = u.hi[w] = 0;
-  }
-  uint32_t both = 0;
+      for (int w = 0; w < Tile<LPP>::W; w++) ts.lo[w] = ts.hi[w] = tu.lo[w] = tu.hi[w] = 0;
+    }
+  };
+  if (kPrefetch && pw < n) fetch(p, s, u);
+  for (; pw < n; pw += stride, p += stride) {
+    const bool valid = p < n;  // invalid groups still take part in the full-warp shuffles
+    if constexpr (kPrefetch) {
+      if (pw + stride < n) fetch(p + stride, ns, nu);
+    } else {
+      fetch(p, s, u);
+    }
+    uint32_t both = 0;
 #pragma unroll
-  for (int w = 0; w < Tile<LPP>::W; w++) both |= (s.lo[w] & u.lo[w]) | (s.hi[w] & u.hi[w]);
-  if (__any_sync(0xffffffffu, both != 0 || force_literal)) {
+    for (int w = 0; w < Tile<LPP>::W; w++) both |= (s.lo[w] & u.lo[w]) | (s.hi[w] & u.hi[w]);
+    if (__any_sync(0xffffffffu, both != 0 || force_literal)) {
 #pragma unroll 1
-    for (unsigned g = 0; g < gens; g++) unknown_step_tile<LPP>(s, u, sub);
-  } else {
-    if constexpr (IL) { s.interleave(); u.interleave(); }
+      for (unsigned g = 0; g < gens; g++) unknown_step_tile<LPP>(s, u, sub);
+    } else {
+      if constexpr (IL) { s.interleave(); u.interleave(); }
 #pragma unroll 1
-    for (unsigned g = 0; g < gens; g++) three_valued_step<LPP, IL>(s, u, sub);
-    if constexpr (IL) { s.deinterleave(); u.deinterleave(); }
-  }
-  if (valid) {
-    s.store(state_out + p * kN, sub);
-    u.store(unknown_out + p * kN, sub);
+      for (unsigned g = 0; g < gens; g++) three_valued_step<LPP, IL>(s, u, sub);
+      if constexpr (IL) { s.deinterleave(); u.deinterleave(); }
+    }
+    if (valid) {
+      s.store(state_out + p * kN, sub);
+      u.store(unknown_out + p * kN, sub);
+    }
+    if constexpr (kPrefetch) { s = ns; u = nu; }
   }
 }
 
@@ -113,14 +131,23 @@ static inline int unknown_lpp(const lifeb200_ctx* ctx) { return ctx->lpp == 0 ? 
 // generation; lifeb200_set_step_layout(1) pins the reference layout, (2) the interleaved one
 constexpr unsigned kUnknownInterleaveFrom = 40;
 
+// one wave of persistent CTAs (or fewer when the batch is small)
+template <typename K>
+static unsigned grid_unknown(const lifeb200_ctx* ctx, K kernel, size_t n, int lpp) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlockU, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  const unsigned resident = (unsigned)(ctx->sm_count > 0 ? ctx->sm_count : 148) * (unsigned)per_sm;
+  return std::min(grid_u(n, lpp), resident);
+}
+
 template <bool IL>
-static int launch_unknown_step_il(cudaStream_t st, int lpp, const uint64_t* si, const uint64_t* ui, uint64_t* so, uint64_t* uo,
-                                  size_t n, unsigned gens, int literal) {
+static int launch_unknown_step_il(const lifeb200_ctx* ctx, cudaStream_t st, int lpp, const uint64_t* si, const uint64_t* ui,
+                                  uint64_t* so, uint64_t* uo, size_t n, unsigned gens, int literal) {
   switch (lpp) {
-    case 4: unknown_step_kernel<4, IL><<<grid_u(n, 4), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
-    case 8: unknown_step_kernel<8, IL><<<grid_u(n, 8), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
-    case 16: unknown_step_kernel<16, IL><<<grid_u(n, 16), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
-    default: unknown_step_kernel<32, IL><<<grid_u(n, 32), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
+    case 4: unknown_step_kernel<4, IL><<<grid_unknown(ctx, unknown_step_kernel<4, IL>, n, 4), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
+    case 8: unknown_step_kernel<8, IL><<<grid_unknown(ctx, unknown_step_kernel<8, IL>, n, 8), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
+    case 16: unknown_step_kernel<16, IL><<<grid_unknown(ctx, unknown_step_kernel<16, IL>, n, 16), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
+    default: unknown_step_kernel<32, IL><<<grid_unknown(ctx, unknown_step_kernel<32, IL>, n, 32), kBlockU, 0, st>>>(si, ui, so, uo, n, gens, literal); break;
   }
   return LIFEB200_OK;
 }
@@ -130,8 +157,8 @@ int launch_unknown_step(lifeb200_ctx* ctx, cudaStream_t st, const uint64_t* si, 
   if (n == 0) return LIFEB200_OK;
   const int lpp = unknown_lpp(ctx);
   const bool il = ctx->step_layout == 0 ? gens >= kUnknownInterleaveFrom : ctx->step_layout >= 2;
-  if (il) launch_unknown_step_il<true>(st, lpp, si, ui, so, uo, n, gens, ctx->unknown_literal);
-  else launch_unknown_step_il<false>(st, lpp, si, ui, so, uo, n, gens, ctx->unknown_literal);
+  if (il) launch_unknown_step_il<true>(ctx, st, lpp, si, ui, so, uo, n, gens, ctx->unknown_literal);
+  else launch_unknown_step_il<false>(ctx, st, lpp, si, ui, so, uo, n, gens, ctx->unknown_literal);
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }
