@@ -16,13 +16,20 @@
 
 namespace lifeb200 {
 
-// 8x8 bit-matrix transpose of a 64-bit word seen as 8 bytes of 8 bits: byte k bit j <-> byte j bit k
-__device__ __forceinline__ uint64_t transpose8x8(uint64_t x) {
-  uint64_t t;
-  t = (x ^ (x >> 7)) & 0x00AA00AA00AA00AAULL; x ^= t ^ (t << 7);
-  t = (x ^ (x >> 14)) & 0x0000CCCC0000CCCCULL; x ^= t ^ (t << 14);
-  t = (x ^ (x >> 28)) & 0x00000000F0F0F0F0ULL; x ^= t ^ (t << 28);
-  return x;
+// Exchange a register-index bit with a position-index bit (a delta swap across a register pair): the bits of
+// `a` at positions with that index bit set trade places with the bits of `b` at positions with it clear
+// (m = positions with the bit clear, d = its weight).  2 SHF + 3 LOP3.
+__device__ __forceinline__ void exchange_bits(uint32_t& a, uint32_t& b, int d, uint32_t m) {
+  const uint32_t t = ((a >> d) ^ b) & m;
+  b ^= t;
+  a ^= t << d;
+}
+// position index bits (p4 p3 p2) = (y4 y3 y5) <-> (y5 y4 y3): swap p2 / p3 (nibbles 1 and 2 of every halfword),
+// then p3 / p4 (bytes 1 and 2).  Either order undoes the other: both steps are involutions and pack / unpack
+// apply them mirrored.  2 SHF + 2 LOP3 + 1 PRMT.
+__device__ __forceinline__ uint32_t swap_nibbles_1_2(uint32_t v) {
+  const uint32_t t = ((v >> 4) ^ v) & 0x00F000F0u;
+  return v ^ t ^ (t << 4);
 }
 
 template <int M>
@@ -80,21 +87,28 @@ struct TileX {
   // words w[s] = column c of pattern s in the reference layout  ->  r[c][0..M-1]
   __device__ __forceinline__ void pack(int c, const uint64_t (&w)[P]) {
     if constexpr (M == 8) {
-      // per pattern: byte k of the transposed word = rows 8j+k (bit j); then the four patterns' bytes k
-      // side by side (bit 8s + j) and two perfect shuffles turn bit 8s + j into bit 4j + s
-      uint32_t tl[P], th[P];
+      // A permutation of index bits: the 8 input registers are numbered (s1 s0 y5) and hold position (y4 .. y0);
+      // the output registers are numbered (y2 y1 y0) and hold position (y5 y4 y3 s1 s0).  Three register <->
+      // position exchanges (s1 <-> y1, s0 <-> y0, y5 <-> y2) put every bit into its register at position
+      // (y4 y3 y5 s1 s0); one nibble swap and one byte swap rotate the top three index bits.  100 integer
+      // instructions per column (12.5 per register) where the 8x8 transposes + byte gathers + two perfect
+      // shuffles per register took about 400.
+      uint32_t x[P][2];
 #pragma unroll
-      for (int s = 0; s < P; s++) {
-        const uint64_t t = transpose8x8(w[s]);
-        tl[s] = (uint32_t)t; th[s] = (uint32_t)(t >> 32);
+      for (int s = 0; s < P; s++) { x[s][0] = (uint32_t)w[s]; x[s][1] = (uint32_t)(w[s] >> 32); }
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        exchange_bits(x[0][h], x[2][h], 2, 0x33333333u);  // s1 <-> y1
+        exchange_bits(x[1][h], x[3][h], 2, 0x33333333u);
+        exchange_bits(x[0][h], x[1][h], 1, 0x55555555u);  // s0 <-> y0
+        exchange_bits(x[2][h], x[3][h], 1, 0x55555555u);
       }
 #pragma unroll
-      for (int k = 0; k < M; k++) {
-        const uint32_t sel = (uint32_t)(k & 3) | ((uint32_t)(4 + (k & 3)) << 4);
-        const uint32_t a = __byte_perm(k < 4 ? tl[0] : th[0], k < 4 ? tl[1] : th[1], sel);
-        const uint32_t b = __byte_perm(k < 4 ? tl[2] : th[2], k < 4 ? tl[3] : th[3], sel);
-        r[c][k] = shuffle32(shuffle32(__byte_perm(a, b, 0x5410)));
-      }
+      for (int s = 0; s < P; s++) exchange_bits(x[s][0], x[s][1], 4, 0x0F0F0F0Fu);  // y5 <-> y2
+#pragma unroll
+      for (int h = 0; h < 2; h++)
+#pragma unroll
+        for (int s = 0; s < P; s++) r[c][4 * h + s] = __byte_perm(swap_nibbles_1_2(x[s][h]), 0, 0x3120);
     } else {
       // M = 4, P = 2: rows 4j+k.  Per pattern: unshuffle twice brings bit 4j+k of each 32-bit half to
       // bit 8k + j (byte k); byte k of the low half = rows 4j+k for j < 8, of the high half for j >= 8.
@@ -116,16 +130,22 @@ struct TileX {
   }
   __device__ __forceinline__ void unpack(int c, uint64_t (&w)[P]) const {
     if constexpr (M == 8) {
-      uint32_t x[M];
+      uint32_t x[P][2];  // pack() run backwards
 #pragma unroll
-      for (int k = 0; k < M; k++) x[k] = unshuffle32(unshuffle32(r[c][k]));  // byte s = pattern s, bit j = row 8j+k
+      for (int h = 0; h < 2; h++)
 #pragma unroll
-      for (int s = 0; s < P; s++) {
-        const uint32_t sel = (uint32_t)s | ((uint32_t)(4 + s) << 4);
-        const uint32_t lo = __byte_perm(__byte_perm(x[0], x[1], sel), __byte_perm(x[2], x[3], sel), 0x5410);
-        const uint32_t hi = __byte_perm(__byte_perm(x[4], x[5], sel), __byte_perm(x[6], x[7], sel), 0x5410);
-        w[s] = transpose8x8(((uint64_t)hi << 32) | lo);
+        for (int s = 0; s < P; s++) x[s][h] = swap_nibbles_1_2(__byte_perm(r[c][4 * h + s], 0, 0x3120));
+#pragma unroll
+      for (int s = 0; s < P; s++) exchange_bits(x[s][0], x[s][1], 4, 0x0F0F0F0Fu);
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        exchange_bits(x[0][h], x[1][h], 1, 0x55555555u);
+        exchange_bits(x[2][h], x[3][h], 1, 0x55555555u);
+        exchange_bits(x[0][h], x[2][h], 2, 0x33333333u);
+        exchange_bits(x[1][h], x[3][h], 2, 0x33333333u);
       }
+#pragma unroll
+      for (int s = 0; s < P; s++) w[s] = ((uint64_t)x[s][1] << 32) | x[s][0];
     } else {
       uint32_t x[M];
 #pragma unroll
