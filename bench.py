@@ -34,9 +34,9 @@ GENS = 1024
 INSTR_PER_CELL = 12.0 / 32.0  # algorithmic 2 SHF + 10 LOP3 per 32 cells per generation
 EXECUTED_INSTR_PER_CELL = 7.75 / 32.0  # what step_kernel_x<8> issues: 4 patterns bit-interleaved per register + pair-shared select
 # dram bytes of one 1 Mi-soup x 1024-generation step_kernel launch from the committed ncu capture
-# (profiles/r01j_step_kernel_x8_raw.csv: dram__bytes_read.sum 543.93 MB + dram__bytes_write.sum 487.77 MB;
+# (profiles/r01z_step_kernel_x8_raw.csv: dram__bytes_read.sum 547.10 MB + dram__bytes_write.sum 489.27 MB;
 # the write side is below 512 MiB because the tail of the output is still in the 126 MB L2 at kernel end)
-STEP_KERNEL_DRAM_BYTES_PER_LAUNCH = 1031704832
+STEP_KERNEL_DRAM_BYTES_PER_LAUNCH = 547099392 + 489269504
 METRIC = "cell_updates_per_sec"
 UNIT = "Gcell/s"
 
