@@ -464,7 +464,8 @@ static void host_zoi(const uint64_t* s, uint64_t* out) {  // LifeAPI.hpp:521-536
 
 // match kernels keep three tiles (state, wanted&mask, mask) in registers: cap W at 16.
 // packing 4 placements costs about 6 generations of stepping
-constexpr unsigned kEnumerateMultiFrom = 48;
+// measured crossovers against the lane-group kernels (profiles/r01z_multi_thresholds.txt)
+constexpr unsigned kEnumerateMultiFrom = 16, kSurveyMultiFrom = 16;
 static inline int match_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
 static inline int survey_lpp(const lifeb200_ctx* ctx) { return std::max(2, effective_lpp(ctx)); }
 
@@ -491,7 +492,34 @@ int lifeb200_step_match_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const u
   return LIFEB200_OK;
 }
 
-static int fetch_hits(lifeb200_ctx* ctx, lifeb200_hit* d_hits, size_t cap, lifeb200_hit* hits, uint64_t* n_hits) {
+// Hit records leave the device in atomic-reservation order; the caller gets them by id.  Ids are unique and lie
+// in [id_lo, id_lo + id_count): when a sizeable share of the range hit (a survey after few generations: most
+// soups are still active) one scatter through a slot table orders them in O(range + found) where std::sort
+// took 15 ms for 512 Ki records; sparse hit lists (the enumeration: thousands of hits in millions of ids) sort.
+static void order_hits(lifeb200_hit* hits, uint64_t found, uint64_t id_lo, uint64_t id_count) {
+  auto by_id = [](const lifeb200_hit& a, const lifeb200_hit& b) { return a.id < b.id; };
+  if (found < 2 || std::is_sorted(hits, hits + found, by_id)) return;
+  if (id_count < 0xFFFFFFFFull && found >= id_count / 16) {
+    std::vector<uint32_t> slot(id_count, 0xFFFFFFFFu);
+    bool ok = true;
+    for (uint64_t i = 0; i < found && ok; i++) {
+      const uint64_t k = hits[i].id - id_lo;
+      ok = k < id_count && slot[k] == 0xFFFFFFFFu;
+      if (ok) slot[k] = (uint32_t)i;
+    }
+    if (ok) {
+      const std::vector<lifeb200_hit> tmp(hits, hits + found);
+      uint64_t o = 0;
+      for (uint64_t k = 0; k < id_count; k++)
+        if (slot[k] != 0xFFFFFFFFu) hits[o++] = tmp[slot[k]];
+      return;
+    }
+  }
+  std::sort(hits, hits + found, by_id);
+}
+
+static int fetch_hits(lifeb200_ctx* ctx, lifeb200_hit* d_hits, size_t cap, lifeb200_hit* hits, uint64_t* n_hits,
+                      uint64_t id_lo, uint64_t id_count) {
   // counters were copied to the pinned mirror and the stream synchronised by the caller
   uint64_t found = ctx->h_counters[0];
   if (n_hits) *n_hits = found;
@@ -500,7 +528,7 @@ static int fetch_hits(lifeb200_ctx* ctx, lifeb200_hit* d_hits, size_t cap, lifeb
   if (found) {
     LIFEB200_CUDA(cudaMemcpyAsync(hits, d_hits, found * sizeof(lifeb200_hit), cudaMemcpyDeviceToHost, ctx->stream));
     LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
-    std::sort(hits, hits + found, [](const lifeb200_hit& a, const lifeb200_hit& b) { return a.id < b.id; });
+    order_hits(hits, found, id_lo, id_count);
   }
   return LIFEB200_OK;
 }
@@ -591,7 +619,7 @@ int lifeb200_enumerate_collisions(lifeb200_ctx* ctx, const uint64_t* catalysts, 
                                   cudaMemcpyDeviceToHost, ctx->stream));
     LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
     if (n_skipped) *n_skipped = ctx->h_counters[1];
-    return fetch_hits(ctx, d_hits, cap, hits, n_hits);
+    return fetch_hits(ctx, d_hits, cap, hits, n_hits, id_begin, id_end - id_begin);
   };
   rc = body();
   return rc;
@@ -616,7 +644,7 @@ int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_
     LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
     // many generations: 4 soups per lane group in the row-class layout (life_multi.cuh), unless the caller
     // pinned the lane grouping or the layout
-    const bool multi = gens >= 96 && ctx->lpp == 0 && (ctx->step_layout == 0 || ctx->step_layout == 8);
+    const bool multi = ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kSurveyMultiFrom));
     if (multi) {
       const size_t groups = (n + 3) / 4;
       survey_kernel_x<8><<<(unsigned)((groups * 8 + 127) / 128), 128, 0, ctx->stream>>>(
@@ -633,7 +661,7 @@ int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_
     LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
     if (pop_sum) *pop_sum = ctx->h_counters[2];
     if (hash_xor) *hash_xor = ctx->h_counters[3];
-    return fetch_hits(ctx, d_hits, cap, hits, n_hits);
+    return fetch_hits(ctx, d_hits, cap, hits, n_hits, first_id, n);
   };
   return body();
 }
