@@ -299,7 +299,9 @@ def main():
         # config 5 shape: each rank surveys its shard of one global id range on device, then the hit
         # lists and counters are gathered over NCCL (the path's only collective)
         from lifeapi_b200 import shard_range
-        total5, gens5 = world << 18, 1024
+        # 2 Mi soups per rank x 4096 generations: at 8 ranks this IS BASELINE config 5 (16 Mi soups), below that the
+        # same per-rank share of it (weak scaling)
+        total5, gens5 = world << 21, 4096
         lo, hi = shard_range(total5, rank, world)
         barrier()
         t0 = time.perf_counter()
@@ -310,7 +312,7 @@ def main():
         torch.cuda.synchronize()
         t_gather = max_over_ranks(time.perf_counter() - t0)
         t_local = max_over_ranks(t_local)
-        survey_gather = {"workload": f"config5 shape: {total5} on-device soups x {gens5} gens sharded by id over {world} ranks",
+        survey_gather = {"workload": f"config5: {total5} on-device soups x {gens5} gens sharded by id over {world} ranks, hit lists gathered over NCCL",
                          "active_hits_total": int(len(merged)), "hits_sorted_unique": bool((np.diff(merged["id"].astype(np.int64)) > 0).all()),
                          "pop_sum": int(sums5[0]), "hash_xor": f"{int(xors5[1]):016x}", "survey_s": t_local,
                          "gather_s": t_gather, "gather_bytes": int(len(merged)) * 16,

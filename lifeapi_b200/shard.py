@@ -89,8 +89,14 @@ def gather_hits(hits: np.ndarray, counters: list[int], device=None, group=None):
         return np.zeros(0, dtype=HIT_DTYPE), sums, xors
     pad = np.zeros(maxc, dtype=HIT_DTYPE)
     pad[: len(hits)] = hits
-    send = torch.from_numpy(pad.view(np.int64).copy()).to(dev)  # 2 x int64 per record
-    recv = [torch.zeros_like(send) for _ in range(world)]
-    dist.all_gather(recv, send, group=group)
-    parts = [r.cpu().numpy().view(HIT_DTYPE)[:c] for r, c in zip(recv, counts)]
+    send = torch.from_numpy(pad.view(np.int64)).to(dev)  # 2 x int64 per record
+    recv = torch.empty(world * send.numel(), dtype=torch.int64, device=dev)
+    try:  # one collective into one buffer, one copy back
+        dist.all_gather_into_tensor(recv, send, group=group)
+    except (RuntimeError, NotImplementedError):  # a backend without the flat form
+        parts_t = [torch.empty_like(send) for _ in range(world)]
+        dist.all_gather(parts_t, send, group=group)
+        recv = torch.cat(parts_t)
+    host = recv.cpu().numpy().view(HIT_DTYPE).reshape(world, maxc)
+    parts = [host[r, :c] for r, c in enumerate(counts)]
     return merge_hits(parts), sums, xors
