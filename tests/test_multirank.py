@@ -73,3 +73,19 @@ def test_gather_hits_world2_gloo():
     ids, pops, ps, hx = Port().survey(0, n, SEED, 0, gens, n)
     assert (merged["id"] == ids).all() and (merged["g_first_false"] == pops).all()
     assert pop_sum == ps and hash_xor == hx
+
+
+def test_bind_host_to_device_is_optional(monkeypatch):
+    """The NUMA binding of one-process-per-GPU runs is an optimisation: without NVML (this container) or when
+    switched off it reports why and leaves the affinity alone."""
+    from lifeapi_b200 import bind_host_to_device
+    before = os.sched_getaffinity(0)
+    monkeypatch.setenv("LIFEB200_NO_NUMA_BIND", "1")
+    assert bind_host_to_device(0).startswith("off")
+    monkeypatch.delenv("LIFEB200_NO_NUMA_BIND")
+    what = bind_host_to_device(0)
+    assert isinstance(what, str) and what
+    if what.startswith("unavailable"):
+        assert os.sched_getaffinity(0) == before
+    else:  # a box with NVML: restore every core for the rest of the session
+        os.sched_setaffinity(0, before)
