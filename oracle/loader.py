@@ -45,7 +45,7 @@ def build_ref() -> bool:
     """Compile the reference where it lies (only possible where /root/reference exists)."""
     if not os.path.isdir("/root/reference"):
         return False
-    subprocess.run(["make", "-C", HERE, "ref"], check=True, stdout=subprocess.DEVNULL)
+    subprocess.run(["make", "-j3", "-C", HERE, "ref"], check=True, stdout=subprocess.DEVNULL)
     return True
 
 
@@ -382,6 +382,18 @@ class Ref:
         _sig(lib, "ref_history_parse", None, [C.c_char_p, _u64p])
         _sig(lib, "ref_match_target_batch", None, [_u64p, C.c_size_t, _u64p, _u64p, C.c_int])
         _sig(lib, "ref_interaction_offsets_batch", None, [_u64p, _u64p, C.c_size_t, _u64p, C.c_int])
+        # native all-thread batch loops (oracle/ref_batch.cpp)
+        _sig(lib, "ref_hash_batch", None, [_u64p, C.c_size_t, _u64p, C.c_int])
+        _sig(lib, "ref_weld_step_batch", None, [_u64p, C.c_size_t, C.c_uint, C.c_int])
+        _sig(lib, "ref_interaction_counts_batch", None, [_u64p, C.c_size_t, _u64p, C.c_int])
+        _sig(lib, "ref_weld_interaction_counts_batch", None, [_u64p, C.c_size_t, _u64p, C.c_int])
+        _sig(lib, "ref_nc_add_batch", None, [_u64p, _u64p, C.c_void_p, C.c_size_t, _u64p, C.c_int])
+        _sig(lib, "ref_nc_subtract_batch", None, [_u64p, _u64p, C.c_size_t, _u64p, C.c_int])
+        _sig(lib, "ref_nc_with_exactly_batch", None, [_u64p, C.c_size_t, C.c_uint, _u64p, C.c_int])
+        _sig(lib, "ref_contains_target_shifted", C.c_int, [_u64p, _u64p, C.c_int, C.c_int])
+        _sig(lib, "ref_enumerate_mt", C.c_size_t, [_u64p, C.c_uint, _u64p, C.c_uint, C.c_uint64, C.c_uint64, C.c_uint, C.c_uint,
+                                                   _u64p, _u32p, _u32p, C.c_size_t, C.POINTER(C.c_uint64), C.c_int])
+        _sig(lib, "ref_survey_states_mt", None, [_u64p, C.c_size_t, C.c_uint, _u8p, _u32p, C.c_int])
 
     _PFX = "ref_"
     _plane_fn = Port._plane_fn
@@ -412,6 +424,78 @@ class Ref:
         out = aligned_copy(np.zeros_like(b))
         self.lib.ref_interaction_offsets_batch(aligned_copy(np.asarray(a).reshape(-1)), b.reshape(-1), b.shape[0], out.reshape(-1), threads)
         return out
+
+    # -- all-thread batch loops over the reference's own members (oracle/ref_batch.cpp) ----------
+    def hash_batch(self, states, threads: int = 0) -> np.ndarray:
+        st = aligned_copy(np.asarray(states, dtype=np.uint64).reshape(-1, 64))
+        out = np.empty(st.shape[0], dtype=np.uint64)
+        self.lib.ref_hash_batch(st.reshape(-1), st.shape[0], out, threads)
+        return out
+
+    def weld_step_batch(self, records, gens: int, threads: int = 0) -> np.ndarray:
+        r = aligned_copy(np.asarray(records, dtype=np.uint64).reshape(-1, 4, 64))
+        self.lib.ref_weld_step_batch(r.reshape(-1), r.shape[0], gens, threads)
+        return r
+
+    def interaction_counts_batch(self, patterns, threads: int = 0) -> np.ndarray:
+        p = aligned_copy(np.asarray(patterns, dtype=np.uint64).reshape(-1, 64))
+        out = aligned_copy(np.zeros((p.shape[0], 4, 64), dtype=np.uint64))
+        self.lib.ref_interaction_counts_batch(p.reshape(-1), p.shape[0], out.reshape(-1), threads)
+        return out
+
+    def weld_interaction_counts_batch(self, records, threads: int = 0) -> np.ndarray:
+        r = aligned_copy(np.asarray(records, dtype=np.uint64).reshape(-1, 4, 64))
+        out = aligned_copy(np.zeros((r.shape[0], 3, 64), dtype=np.uint64))
+        self.lib.ref_weld_interaction_counts_batch(r.reshape(-1), r.shape[0], out.reshape(-1), threads)
+        return out
+
+    def nc_add_batch(self, a, b, incarry=None, threads: int = 0) -> np.ndarray:
+        a = aligned_copy(np.asarray(a, dtype=np.uint64).reshape(-1, 4, 64))
+        b = aligned_copy(np.asarray(b, dtype=np.uint64).reshape(-1, 4, 64))
+        out = aligned_copy(np.zeros_like(a))
+        ic = None
+        if incarry is not None:
+            ic = aligned_copy(np.asarray(incarry, dtype=np.uint64).reshape(-1, 64))
+        self.lib.ref_nc_add_batch(a.reshape(-1), b.reshape(-1), ic.ctypes.data if ic is not None else None, a.shape[0],
+                                  out.reshape(-1), threads)
+        return out
+
+    def nc_subtract_batch(self, a, b, threads: int = 0) -> np.ndarray:
+        a = aligned_copy(np.asarray(a, dtype=np.uint64).reshape(-1, 4, 64))
+        b = aligned_copy(np.asarray(b, dtype=np.uint64).reshape(-1, 4, 64))
+        out = aligned_copy(np.zeros_like(a))
+        self.lib.ref_nc_subtract_batch(a.reshape(-1), b.reshape(-1), a.shape[0], out.reshape(-1), threads)
+        return out
+
+    def nc_with_exactly_batch(self, a, k: int, threads: int = 0) -> np.ndarray:
+        a = aligned_copy(np.asarray(a, dtype=np.uint64).reshape(-1, 4, 64))
+        out = aligned_copy(np.zeros((a.shape[0], 64), dtype=np.uint64))
+        self.lib.ref_nc_with_exactly_batch(a.reshape(-1), a.shape[0], k, out.reshape(-1), threads)
+        return out
+
+    def contains_target_shifted(self, s, target, dx: int, dy: int) -> bool:
+        return bool(self.lib.ref_contains_target_shifted(aligned_copy(np.asarray(s, dtype=np.uint64).reshape(-1)),
+                                                         aligned_copy(np.asarray(target, dtype=np.uint64).reshape(-1)), dx, dy))
+
+    def enumerate_mt(self, catalysts, projectiles, id_begin, id_end, gens, stable_interval, cap, threads: int = 0):
+        cat = aligned_copy(np.asarray(catalysts, dtype=np.uint64).reshape(-1))
+        pro = aligned_copy(np.asarray(projectiles, dtype=np.uint64).reshape(-1))
+        ids = np.zeros(max(cap, 1), dtype=np.uint64)
+        ff = np.zeros(max(cap, 1), dtype=np.uint32)
+        rec = np.zeros(max(cap, 1), dtype=np.uint32)
+        ns = C.c_uint64()
+        nh = self.lib.ref_enumerate_mt(cat, cat.size // 64, pro, pro.size // 64, id_begin, id_end, gens, stable_interval,
+                                       ids, ff, rec, cap, C.byref(ns), threads)
+        nh = min(nh, cap)
+        return ids[:nh], ff[:nh], rec[:nh], ns.value
+
+    def survey_states_mt(self, states, gens, threads: int = 0):
+        st = aligned_copy(np.asarray(states, dtype=np.uint64).reshape(-1, 64))
+        n = st.shape[0]
+        act = np.zeros(n, dtype=np.uint8)
+        pop = np.zeros(n, dtype=np.uint32)
+        self.lib.ref_survey_states_mt(st.reshape(-1), n, gens, act, pop, threads)
+        return st, act, pop
 
     def isa(self) -> str:
         return self.lib.ref_isa().decode()
