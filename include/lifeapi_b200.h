@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define LIFEB200_ABI_VERSION 2
+#define LIFEB200_ABI_VERSION 3
 #define LIFEB200_WORDS 64          /* LifeAPI.hpp:12  const int N = 64 */
 #define LIFEB200_PATTERN_BYTES 512 /* sizeof(LifeState) */
 
@@ -36,7 +36,8 @@ enum {
   LIFEB200_E_CUDA = 1,      /* CUDA runtime error (message has the cudaError string) */
   LIFEB200_E_ARG = 2,       /* bad argument (null / misaligned pointer, bad enum) */
   LIFEB200_E_OVERFLOW = 3,  /* hit buffer too small: *n_hits holds the required count */
-  LIFEB200_E_NODEVICE = 4   /* no CUDA device / wrong architecture */
+  LIFEB200_E_NODEVICE = 4,  /* no CUDA device / wrong architecture */
+  LIFEB200_E_NCCL = 5       /* NCCL could not be loaded or a collective failed (multi-GPU groups only) */
 };
 
 typedef struct lifeb200_ctx lifeb200_ctx; /* opaque: device, stream, scratch, pinned staging */
@@ -103,9 +104,9 @@ typedef struct lifeb200_hit {
  * (targets: n_targets x {wanted[64], unwanted[64]} = 1024 B each, LifeTarget.hpp:5-7; a NULL
  * target_index means target 0 for all): step up to `gens` generations evaluating Contains at every
  * generation; a HIT is a pattern whose predicate was false at some generation >= 1 and later
- * true for `stable_interval` consecutive generations.  Hits are compacted (warp ballot + one
- * atomic per warp) into `hits` (device, capacity `cap`); *n_hits (device) receives the count.
- * Patterns are not written back.  first_id is added to p in the reported id. */
+ * true for `stable_interval` consecutive generations.  Hits are compacted (dense per-id results + scan,
+ * in id order, no sort: csrc/match.cu) into `hits` (device, capacity `cap`); *n_hits (device) receives the
+ * count.  Patterns are not written back.  first_id is added to p in the reported id. */
 int lifeb200_step_match_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const uint64_t* targets,
                             const uint32_t* target_index, size_t n, uint64_t first_id, unsigned gens,
                             unsigned stable_interval, lifeb200_hit* hits, size_t cap,
@@ -134,6 +135,16 @@ int lifeb200_enumerate_collisions(lifeb200_ctx* ctx, const uint64_t* catalysts, 
 int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t seed, int dist,
                          unsigned gens, lifeb200_hit* hits, size_t cap, uint64_t* n_hits,
                          uint64_t* pop_sum, uint64_t* hash_xor);
+/* Device-resident forms of the two calls above: `d_hits` is a DEVICE buffer of `cap` records on the context's
+ * GPU; the records are left there sorted by id (for a gather over NVLink, lifeb200_multi_* below, or a caller's
+ * own collective) and only the counters come back to the host.  The calls synchronise the stream. */
+int lifeb200_enumerate_collisions_dev(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts,
+                                      const uint64_t* projectiles, unsigned n_projectiles, uint64_t id_begin,
+                                      uint64_t id_end, unsigned gens, unsigned stable_interval, lifeb200_hit* d_hits,
+                                      size_t cap, uint64_t* n_hits, uint64_t* n_skipped);
+int lifeb200_soup_survey_dev(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t seed, int dist, unsigned gens,
+                             lifeb200_hit* d_hits, size_t cap, uint64_t* n_hits, uint64_t* pop_sum,
+                             uint64_t* hash_xor);
 /* The same 64-bit fold of a resident batch: XOR over patterns of fold(p). */
 int lifeb200_fold_dev(lifeb200_ctx* ctx, const uint64_t* patterns, size_t n, uint64_t first_id,
                       uint64_t* pop_sum, uint64_t* hash_xor);
@@ -251,6 +262,44 @@ int lifeb200_rle(const uint64_t* state, char* buf, size_t cap, size_t* len);
 int lifeb200_history_rle(const uint64_t* record, char* buf, size_t cap, size_t* len);
 int lifeb200_parse_rle(const char* rle, uint64_t* state);
 int lifeb200_history_parse_rle(const char* rle, uint64_t* record);
+
+/* ---- multi-GPU groups (SURVEY.md 8b "device management (init with device list)", "multi-GPU run + gather";
+ * 8e).  The reference is single-threaded; the loop a caller shards is LifeAPI.hpp:877-881.  A group is `world`
+ * ranks, one GPU each; rank r owns the contiguous id range [first + n*r/world, first + n*(r+1)/world) of every
+ * call.  The path has no exchange step, so the only collective is the gather of hit lists and counters over
+ * NCCL (csrc/multi.cu).  Every process of the group makes the same calls with the same GLOBAL arguments;
+ * counters come back on every rank, the merged hit list (sorted by id) on the process that owns rank 0.
+ *   lifeb200_multi_create        all ranks in THIS process: devices[0..n) (NULL = 0..n-1; n <= 0 with NULL = every
+ *                                visible GPU), ncclCommInitAll, one host thread per GPU inside the calls
+ *   lifeb200_multi_unique_id /   one process per GPU (torchrun / MPI): rank 0 makes a 128-byte id, the caller
+ *   lifeb200_multi_create_rank   distributes it, every process joins with its device, rank and world
+ * NCCL is loaded at run time (libnccl.so.2 or $LIFEB200_NCCL_LIB); a group of one needs none. */
+#define LIFEB200_UNIQUE_ID_BYTES 128
+typedef struct lifeb200_multi lifeb200_multi;
+int lifeb200_multi_create(const int* devices, int n_devices, lifeb200_multi** out);
+int lifeb200_multi_unique_id(char* id128);
+int lifeb200_multi_create_rank(int device, int rank, int world, const char* id128, lifeb200_multi** out);
+int lifeb200_multi_destroy(lifeb200_multi* m);
+int lifeb200_multi_info(lifeb200_multi* m, int* world, int* first_rank, int* n_local, int* nccl_version);
+/* Borrow the context of local GPU `local_index` (owned by the group) for per-device calls. */
+int lifeb200_multi_ctx(lifeb200_multi* m, int local_index, lifeb200_ctx** ctx);
+int lifeb200_multi_sync(lifeb200_multi* m);
+/* The id range rank `rank` owns of a call over [first_id, first_id + n). */
+int lifeb200_multi_shard(lifeb200_multi* m, uint64_t first_id, uint64_t n, int rank, uint64_t* begin, uint64_t* end);
+/* How hit lists reach the host: 0 = NCCL send/recv over NVLink into rank 0's GPU, one download (default);
+ * 1 = every GPU downloads its list straight to its place in `hits` (groups created by lifeb200_multi_create only). */
+int lifeb200_multi_set_gather(lifeb200_multi* m, int mode);
+/* Device time of the last call's gather (counters + hit lists + download), CUDA events on local GPU 0. */
+int lifeb200_multi_last_gather_ms(lifeb200_multi* m, float* ms);
+/* lifeb200_soup_survey / lifeb200_enumerate_collisions over the whole group (same arguments, HOST hit buffer). */
+int lifeb200_multi_soup_survey(lifeb200_multi* m, uint64_t first_id, uint64_t n, uint64_t seed, int dist, unsigned gens,
+                               lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* pop_sum, uint64_t* hash_xor);
+int lifeb200_multi_enumerate_collisions(lifeb200_multi* m, const uint64_t* catalysts, unsigned n_catalysts,
+                                        const uint64_t* projectiles, unsigned n_projectiles, uint64_t id_begin,
+                                        uint64_t id_end, unsigned gens, unsigned stable_interval, lifeb200_hit* hits,
+                                        size_t cap, uint64_t* n_hits, uint64_t* n_skipped);
+/* lifeb200_step_batch_host with THIS process's n patterns split over its local GPUs (one host thread each). */
+int lifeb200_multi_step_batch_host(lifeb200_multi* m, const uint64_t* in, uint64_t* out, size_t n, unsigned gens);
 
 /* ---- roofline denominator: measured LOP3 lane-instructions per second ------------------- */
 int lifeb200_measure_int_peak(lifeb200_ctx* ctx, double* lop3_lane_instr_per_s, double* sm_mhz_effective);

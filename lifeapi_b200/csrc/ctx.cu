@@ -44,8 +44,14 @@ int ensure_scratch(void*& buf, size_t& cap, size_t bytes) {
   if (cap >= bytes) return LIFEB200_OK;
   if (buf) LIFEB200_CUDA(cudaFree(buf));  // synchronises the device: earlier users of the block are done
   buf = nullptr; cap = 0;
-  LIFEB200_CUDA(cudaMalloc(&buf, bytes));
-  cap = bytes;
+  // grow by at least half so that a caller walking through slightly larger batches reallocates O(log) times
+  size_t want = bytes + bytes / 2;
+  if (cudaMalloc(&buf, want) != cudaSuccess) {
+    (void)cudaGetLastError();
+    want = bytes;
+    LIFEB200_CUDA(cudaMalloc(&buf, want));
+  }
+  cap = want;
   return LIFEB200_OK;
 }
 
@@ -111,6 +117,8 @@ int lifeb200_destroy(lifeb200_ctx* c) {
   }
   if (c->d_hitbuf) cudaFree(c->d_hitbuf);
   if (c->d_tabbuf) cudaFree(c->d_tabbuf);
+  if (c->d_dense) cudaFree(c->d_dense);
+  if (c->d_tiles) cudaFree(c->d_tiles);
   if (c->d_counters) cudaFree(c->d_counters);
   if (c->h_counters) cudaFreeHost(c->h_counters);
   if (c->ev_start) cudaEventDestroy(c->ev_start);

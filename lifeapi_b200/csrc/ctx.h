@@ -45,6 +45,15 @@ struct lifeb200_ctx {
   size_t hitbuf_cap = 0;
   void* d_tabbuf = nullptr;
   size_t tabbuf_cap = 0;
+  // the enumeration tables in d_tabbuf are kept across calls, keyed by a hash of their words (csrc/match.cu)
+  bool tab_valid = false;
+  uint64_t tab_key = 0;
+  unsigned tab_ncat = 0, tab_nproj = 0;
+  // dense per-id results (8 B per id) and per-tile hit counts of the ordered compaction (csrc/match.cu)
+  void* d_dense = nullptr;
+  size_t dense_cap = 0;
+  void* d_tiles = nullptr;
+  size_t tiles_cap = 0;
 };
 
 namespace lifeb200 {
@@ -53,6 +62,14 @@ int set_error(int code, const char* fmt, ...);
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 int ensure_slot(lifeb200_ctx* ctx, int slot, size_t bytes, size_t bytes2);
 int ensure_scratch(void*& buf, size_t& cap, size_t bytes);  // grow-only; the old block is released after a stream sync
+
+// csrc/match.cu: run one shard, leave the hit records sorted by id in d_hits (capacity cap) and the counters
+// n_hits, n_skipped, pop_sum, hash_xor in ctx->d_counters[0..3] AND ctx->h_counters[0..3]; the stream is synchronised
+int survey_to_device(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t seed, int dist, unsigned gens,
+                     lifeb200_hit* d_hits, size_t cap);
+int enumerate_to_device(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts, const uint64_t* projectiles,
+                        unsigned n_projectiles, uint64_t id_begin, uint64_t id_end, unsigned gens, unsigned stable_interval,
+                        lifeb200_hit* d_hits, size_t cap);
 
 #define LIFEB200_CUDA(expr)                                                        \
   do {                                                                             \
@@ -87,6 +104,18 @@ inline int effective_lpp(const lifeb200_ctx* ctx) { return ctx->lpp ? ctx->lpp :
     case 16: { constexpr int LPP = 16; CALL; } break; \
     case 32: { constexpr int LPP = 32; CALL; } break; \
     default: return lifeb200::set_error(LIFEB200_E_ARG, "lanes per pattern must be 1,2,4,8,16,32"); \
+  }
+
+// the same for kernels that keep three or more tiles in registers: with 1 or 2 lanes per pattern (64 / 32 words
+// per lane and tile) they only measured register spills (1.2 k LDL/STL per kernel), so those instantiations
+// are not built; callers clamp the lane grouping to 4..32 first
+#define LIFEB200_DISPATCH_LPP_MIN4(lpp, CALL) \
+  switch (lpp) {                              \
+    case 4: { constexpr int LPP = 4; CALL; } break;   \
+    case 8: { constexpr int LPP = 8; CALL; } break;   \
+    case 16: { constexpr int LPP = 16; CALL; } break; \
+    case 32: { constexpr int LPP = 32; CALL; } break; \
+    default: return lifeb200::set_error(LIFEB200_E_ARG, "lanes per pattern must be 4,8,16,32 for this kernel"); \
   }
 
 }  // namespace lifeb200

@@ -41,24 +41,118 @@ struct Recovery {
   }
 };
 
-// Warp-aggregated append: one atomicAdd per warp, hits beyond `cap` are counted but not written.
-__device__ __forceinline__ void append_hit(bool emit, uint64_t id, uint32_t a, uint32_t b, lifeb200_hit* hits,
-                                           size_t cap, unsigned long long* n_hits) {
-  unsigned m = __ballot_sync(0xffffffffu, emit);
-  if (m == 0) return;
-  int lane = threadIdx.x & 31;
-  int leader = __ffs(m) - 1;
-  unsigned long long base = 0;
-  if (lane == leader) base = atomicAdd(n_hits, (unsigned long long)__popc(m));
-  base = __shfl_sync(0xffffffffu, base, leader);
-  if (emit) {
-    unsigned long long slot = base + __popc(m & ((1u << lane) - 1u));
-    if (slot < cap) {
-      lifeb200_hit h;
-      h.id = id; h.g_first_false = a; h.g_recovered = b;
-      hits[slot] = h;
-    }
+// Hit records leave the kernels in ID ORDER without a sort: every id writes one 64-bit word of a dense result
+// array (bit 63 = hit, bits 32..62 = b, bits 0..31 = a), and three small launches compact it -- per-tile hit
+// counts, an exclusive scan of the tile counts, a scatter in which every thread owns 8 consecutive ids.  The
+// order is the id order by construction (deterministic, unlike atomic slot reservation), hits beyond `cap` are
+// counted but not written, and the list can stay on the device for the gather (8 bytes per id of scratch: 16 Mi
+// soups = 128 MiB; the three launches move 2 x 8 bytes per id, about 10 us per 2 Mi ids).
+__device__ __forceinline__ uint64_t dense_record(bool hit, uint32_t a, uint32_t b) {
+  return hit ? (1ull << 63) | ((uint64_t)(b & 0x7FFFFFFFu) << 32) | a : 0ull;
+}
+
+constexpr int kCompactThreads = 256, kCompactPer = 8, kCompactTile = kCompactThreads * kCompactPer;
+
+__device__ __forceinline__ uint32_t compact_load(const uint64_t* __restrict__ dense, size_t n, size_t base, uint64_t (&v)[kCompactPer]) {
+  uint32_t c = 0;
+#pragma unroll
+  for (int k = 0; k < kCompactPer; k += 2) {
+    ulonglong2 w = make_ulonglong2(0, 0);
+    if (base + k + 1 < n) w = *reinterpret_cast<const ulonglong2*>(dense + base + k);
+    else if (base + k < n) w.x = dense[base + k];
+    v[k] = w.x; v[k + 1] = w.y;
+    c += (uint32_t)(w.x >> 63) + (uint32_t)(w.y >> 63);
   }
+  return c;
+}
+
+// exclusive prefix of `c` over the CTA's threads in thread order; *total = the CTA's sum
+__device__ __forceinline__ uint32_t block_exclusive(uint32_t c, uint32_t* total) {
+  __shared__ uint32_t warp_sum[kCompactThreads / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t inc = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) warp_sum[warp] = inc;
+  __syncthreads();
+  uint32_t before = 0, all = 0;
+#pragma unroll
+  for (int w = 0; w < kCompactThreads / 32; w++) {
+    const uint32_t t = warp_sum[w];
+    if (w < warp) before += t;
+    all += t;
+  }
+  *total = all;
+  return before + inc - c;
+}
+
+__global__ void __launch_bounds__(kCompactThreads) compact_count_kernel(const uint64_t* __restrict__ dense, size_t n,
+                                                                         unsigned long long* __restrict__ tile_base) {
+  uint64_t v[kCompactPer];
+  const uint32_t c = compact_load(dense, n, (size_t)blockIdx.x * kCompactTile + threadIdx.x * kCompactPer, v);
+  uint32_t total;
+  block_exclusive(c, &total);
+  if (threadIdx.x == 0) tile_base[blockIdx.x] = total;
+}
+
+// one CTA: tile counts -> exclusive bases in place, the grand total -> *n_hits
+__global__ void __launch_bounds__(1024) compact_scan_kernel(unsigned long long* __restrict__ tile_base, size_t n_tiles,
+                                                            unsigned long long* __restrict__ n_hits) {
+  __shared__ unsigned long long warp_sum[32];
+  __shared__ unsigned long long carry_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (size_t off = 0; off < n_tiles; off += 1024) {
+    const size_t i = off + threadIdx.x;
+    const unsigned long long c = i < n_tiles ? tile_base[i] : 0ull;
+    unsigned long long inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned long long t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_sum[warp] = inc;
+    __syncthreads();
+    unsigned long long before = carry_s, all = 0;
+    for (int w = 0; w < 32; w++) {
+      const unsigned long long t = warp_sum[w];
+      if (w < warp) before += t;
+      all += t;
+    }
+    if (i < n_tiles) tile_base[i] = before + inc - c;
+    __syncthreads();
+    if (threadIdx.x == 0) carry_s += all;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *n_hits = carry_s;
+}
+
+__global__ void __launch_bounds__(kCompactThreads) compact_scatter_kernel(const uint64_t* __restrict__ dense, size_t n,
+                                                                           const unsigned long long* __restrict__ tile_base,
+                                                                           uint64_t first_id, lifeb200_hit* __restrict__ hits,
+                                                                           size_t cap) {
+  uint64_t v[kCompactPer];
+  const size_t base = (size_t)blockIdx.x * kCompactTile + threadIdx.x * kCompactPer;
+  const uint32_t c = compact_load(dense, n, base, v);
+  uint32_t total;
+  unsigned long long slot = tile_base[blockIdx.x] + block_exclusive(c, &total);
+  if (c == 0) return;
+#pragma unroll
+  for (int k = 0; k < kCompactPer; k++)
+    if (v[k] >> 63) {
+      if (slot < cap) {
+        lifeb200_hit h;
+        h.id = first_id + base + k;
+        h.g_first_false = (uint32_t)v[k];
+        h.g_recovered = (uint32_t)(v[k] >> 32) & 0x7FFFFFFFu;
+        hits[slot] = h;
+      }
+      slot++;
+    }
 }
 
 template <int LPP>
@@ -83,8 +177,8 @@ template <int LPP>
 __global__ void __launch_bounds__(kBlockM, 1) step_match_kernel(const uint64_t* __restrict__ patterns,
                                                              const uint64_t* __restrict__ targets,
                                                              const uint32_t* __restrict__ target_index, size_t n,
-                                                             uint64_t first_id, unsigned gens, unsigned stable_interval,
-                                                             lifeb200_hit* hits, size_t cap, unsigned long long* n_hits) {
+                                                             unsigned gens, unsigned stable_interval,
+                                                             uint64_t* __restrict__ dense) {
   constexpr int W = Tile<LPP>::W;
   const size_t gid = (size_t)blockIdx.x * kBlockM + threadIdx.x;
   const size_t p = gid / LPP;
@@ -107,7 +201,7 @@ __global__ void __launch_bounds__(kBlockM, 1) step_match_kernel(const uint64_t* 
     r.done = true;
   }
   run_match<LPP>(t, wm, m, sub, lane, gens, stable_interval, r);
-  append_hit(valid && r.hit && sub == 0, first_id + p, r.first_false, r.recovered, hits, cap, n_hits);
+  if (valid && sub == 0) dense[p] = dense_record(r.hit, r.first_false, r.recovered);
 }
 
 __device__ __forceinline__ uint64_t rotl64v(uint64_t v, unsigned s) {
@@ -122,8 +216,8 @@ __global__ void __launch_bounds__(kBlockM, 1) enumerate_kernel(const uint64_t* _
                                                             const uint64_t* __restrict__ proj,
                                                             const uint64_t* __restrict__ proj_zoi, unsigned n_proj,
                                                             uint64_t id_begin, uint64_t id_end, unsigned gens,
-                                                            unsigned stable_interval, lifeb200_hit* hits, size_t cap,
-                                                            unsigned long long* n_hits, unsigned long long* n_skipped) {
+                                                            unsigned stable_interval, uint64_t* __restrict__ dense,
+                                                            unsigned long long* n_skipped) {
   constexpr int W = Tile<LPP>::W;
   const uint64_t gid = (uint64_t)blockIdx.x * kBlockM + threadIdx.x;
   const uint64_t id = id_begin + gid / LPP;
@@ -166,7 +260,7 @@ __global__ void __launch_bounds__(kBlockM, 1) enumerate_kernel(const uint64_t* _
     if (lane == 0 && sk) atomicAdd(n_skipped, (unsigned long long)__popc(sk));
   }
   run_match<LPP>(t, wm, m, sub, lane, gens, stable_interval, r);
-  append_hit(valid && r.hit && sub == 0, id, r.first_false, r.recovered, hits, cap, n_hits);
+  if (valid && sub == 0) dense[id - id_begin] = dense_record(r.hit, r.first_false, r.recovered);
 }
 
 // The same enumeration with 4 placements per group of 8 lanes in the row-class layout (life_multi.cuh).
@@ -194,8 +288,8 @@ __global__ void __launch_bounds__(128, 1) enumerate_kernel_x(const uint64_t* __r
                                                              const uint32_t* __restrict__ packed_wanted,
                                                              const uint32_t* __restrict__ packed_mask, unsigned n_proj,
                                                              uint64_t id_begin, uint64_t id_end, unsigned gens,
-                                                             unsigned stable_interval, lifeb200_hit* hits, size_t cap,
-                                                             unsigned long long* n_hits, unsigned long long* n_skipped) {
+                                                             unsigned stable_interval, uint64_t* __restrict__ dense,
+                                                             unsigned long long* n_skipped) {
   constexpr int M = 8, P = 4;
   const uint64_t gid = (uint64_t)blockIdx.x * 128 + threadIdx.x;
   const uint64_t base = (id_begin & ~3ull) + (gid >> 3) * P;
@@ -302,7 +396,7 @@ __global__ void __launch_bounds__(128, 1) enumerate_kernel_x(const uint64_t* __r
     const uint32_t all = group8_or(d_prev);
     r.observe_flat((all & (0x11111111u << mine)) != 0, gens, stable_interval);
   }
-  append_hit(valid && r.hit && sub < P, id, r.first_false, r.recovered, hits, cap, n_hits);
+  if (valid && sub < P) dense[id - id_begin] = dense_record(r.hit, r.first_false, r.recovered);
 }
 
 // Per-pattern 64-bit fold used as a size-independent checksum (build-defined):
@@ -338,9 +432,8 @@ __device__ __forceinline__ void block_accumulate(uint64_t pop, uint64_t h, unsig
 
 template <int LPP>
 __global__ void __launch_bounds__(kBlockM, 1) survey_kernel(uint64_t first_id, size_t n, uint64_t seed, int dist,
-                                                         unsigned gens, lifeb200_hit* hits, size_t cap,
-                                                         unsigned long long* n_hits, unsigned long long* pop_sum,
-                                                         unsigned long long* hash_xor) {
+                                                         unsigned gens, uint64_t* __restrict__ dense,
+                                                         unsigned long long* pop_sum, unsigned long long* hash_xor) {
   constexpr int W = Tile<LPP>::W;
   const size_t gid = (size_t)blockIdx.x * kBlockM + threadIdx.x;
   const size_t p = gid / LPP;
@@ -365,14 +458,14 @@ __global__ void __launch_bounds__(kBlockM, 1) survey_kernel(uint64_t first_id, s
   const uint64_t f = group_fold<LPP>(t, sub);
   const bool leader = valid && sub == 0;
   block_accumulate(leader ? pop : 0u, leader ? splitmix64(f + id) : 0ULL, pop_sum, hash_xor);
-  append_hit(leader && active, id, pop, 0u, hits, cap, n_hits);
+  if (leader) dense[p] = dense_record(active, pop, 0u);
 }
 
 // The same survey with P = M/2 soups per group of 8 lanes in the row-class layout (life_multi.cuh).
 template <int M>
 __global__ void __launch_bounds__(128, 1) survey_kernel_x(uint64_t first_id, size_t n, uint64_t seed, int dist, unsigned gens,
-                                                          lifeb200_hit* hits, size_t cap, unsigned long long* n_hits,
-                                                          unsigned long long* pop_sum, unsigned long long* hash_xor) {
+                                                          uint64_t* __restrict__ dense, unsigned long long* pop_sum,
+                                                          unsigned long long* hash_xor) {
   constexpr int P = M / 2;
   const size_t gid = (size_t)blockIdx.x * 128 + threadIdx.x;
   const size_t p0 = (gid >> 3) * P;
@@ -431,7 +524,7 @@ __global__ void __launch_bounds__(128, 1) survey_kernel_x(uint64_t first_id, siz
   const bool leader = sub < P && p0 + sub < n;
   const uint64_t id = first_id + p0 + sub;
   block_accumulate(leader ? my_pop : 0u, leader ? splitmix64(my_f + id) : 0ULL, pop_sum, hash_xor);
-  append_hit(leader && my_diff != 0, id, my_pop, 0u, hits, cap, n_hits);
+  if (leader) dense[p0 + sub] = dense_record(my_diff != 0, my_pop, 0u);
 }
 
 template <int LPP>
@@ -467,7 +560,158 @@ static void host_zoi(const uint64_t* s, uint64_t* out) {  // LifeAPI.hpp:521-536
 // measured crossovers against the lane-group kernels (profiles/r01z_multi_thresholds.txt)
 constexpr unsigned kEnumerateMultiFrom = 16, kSurveyMultiFrom = 16;
 static inline int match_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
-static inline int survey_lpp(const lifeb200_ctx* ctx) { return std::max(2, effective_lpp(ctx)); }
+static inline int survey_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
+
+// dense result scratch of a call over `n` ids (context-owned, grow-only)
+static int ensure_dense(lifeb200_ctx* ctx, size_t n) {
+  if (int rc = ensure_scratch(ctx->d_dense, ctx->dense_cap, n * sizeof(uint64_t))) return rc;
+  const size_t tiles = (n + kCompactTile - 1) / kCompactTile;
+  return ensure_scratch(ctx->d_tiles, ctx->tiles_cap, tiles * sizeof(unsigned long long));
+}
+
+// dense[0..n) -> hits[0..min(found, cap)) in id order, found -> *d_n_hits (device); three launches on the stream
+static int compact_hits(lifeb200_ctx* ctx, size_t n, uint64_t first_id, lifeb200_hit* d_hits, size_t cap,
+                        unsigned long long* d_n_hits) {
+  const uint64_t* dense = static_cast<const uint64_t*>(ctx->d_dense);
+  unsigned long long* tiles = static_cast<unsigned long long*>(ctx->d_tiles);
+  const size_t n_tiles = (n + kCompactTile - 1) / kCompactTile;
+  compact_count_kernel<<<(unsigned)n_tiles, kCompactThreads, 0, ctx->stream>>>(dense, n, tiles);
+  LIFEB200_LAUNCHED(ctx);
+  compact_scan_kernel<<<1, 1024, 0, ctx->stream>>>(tiles, n_tiles, d_n_hits);
+  LIFEB200_LAUNCHED(ctx);
+  compact_scatter_kernel<<<(unsigned)n_tiles, kCompactThreads, 0, ctx->stream>>>(dense, n, tiles, first_id, d_hits, cap);
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+static uint64_t table_key(const uint64_t* a, size_t na, const uint64_t* b, size_t nb) {  // FNV-1a style over the words
+  uint64_t h = 0xCBF29CE484222325ull;
+  auto mix = [&h](const uint64_t* p, size_t n) {
+    for (size_t i = 0; i < n; i++) { h ^= p[i]; h *= 0x100000001B3ull; h ^= h >> 29; }
+  };
+  mix(a, na); mix(b, nb);
+  return h ^ ((uint64_t)na << 32) ^ nb;
+}
+
+// Enumeration tables on the device: cat | catZOI | proj | projZOI (64 words each) followed by the layout-8 target
+// planes (every cell of wanted = catalyst and of mask = its ZOI replicated into the four pattern bits of register
+// (column, k)).  Built and uploaded once per distinct table content: a sharded caller walks one table set over
+// many id ranges, and the context keeps the last set keyed by a hash of its words.
+static int ensure_tables(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts, const uint64_t* projectiles,
+                         unsigned n_projectiles) {
+  const uint64_t key = table_key(catalysts, (size_t)n_catalysts * 64, projectiles, (size_t)n_projectiles * 64);
+  if (ctx->tab_valid && ctx->tab_key == key && ctx->tab_ncat == n_catalysts && ctx->tab_nproj == n_projectiles)
+    return LIFEB200_OK;
+  ctx->tab_valid = false;
+  const size_t words = (size_t)(n_catalysts + n_projectiles) * 2 * 64;
+  const size_t packed_words = (size_t)n_catalysts * 64 * 8 * 2;
+  std::vector<uint64_t> tab(words);
+  uint64_t* h_cat = tab.data();
+  uint64_t* h_cz = h_cat + (size_t)n_catalysts * 64;
+  uint64_t* h_pr = h_cz + (size_t)n_catalysts * 64;
+  uint64_t* h_pz = h_pr + (size_t)n_projectiles * 64;
+  std::copy(catalysts, catalysts + (size_t)n_catalysts * 64, h_cat);
+  std::copy(projectiles, projectiles + (size_t)n_projectiles * 64, h_pr);
+  for (unsigned c = 0; c < n_catalysts; c++) host_zoi(h_cat + (size_t)c * 64, h_cz + (size_t)c * 64);
+  for (unsigned g = 0; g < n_projectiles; g++) host_zoi(h_pr + (size_t)g * 64, h_pz + (size_t)g * 64);
+  std::vector<uint32_t> packed(packed_words);
+  uint32_t* pk_w = packed.data();
+  uint32_t* pk_m = pk_w + (size_t)n_catalysts * 64 * 8;
+  for (size_t ci = 0; ci < (size_t)n_catalysts * 64; ci++)
+    for (int k = 0; k < 8; k++) {
+      uint32_t w = 0, m = 0;
+      for (int j = 0; j < 8; j++) {
+        if (h_cat[ci] >> (8 * j + k) & 1) w |= 0xFu << (4 * j);
+        if (h_cz[ci] >> (8 * j + k) & 1) m |= 0xFu << (4 * j);
+      }
+      pk_w[ci * 8 + k] = w;
+      pk_m[ci * 8 + k] = m;
+    }
+  if (int rc = ensure_scratch(ctx->d_tabbuf, ctx->tabbuf_cap, words * 8 + packed_words * 4)) return rc;
+  uint64_t* d_tab = static_cast<uint64_t*>(ctx->d_tabbuf);
+  // pageable sources: the stream is synchronised before `tab` / `packed` go out of scope
+  LIFEB200_CUDA(cudaMemcpyAsync(d_tab, tab.data(), words * 8, cudaMemcpyHostToDevice, ctx->stream));
+  LIFEB200_CUDA(cudaMemcpyAsync(d_tab + words, packed.data(), packed_words * 4, cudaMemcpyHostToDevice, ctx->stream));
+  LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+  ctx->tab_key = key; ctx->tab_ncat = n_catalysts; ctx->tab_nproj = n_projectiles; ctx->tab_valid = true;
+  return LIFEB200_OK;
+}
+
+int enumerate_to_device(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts, const uint64_t* projectiles,
+                        unsigned n_projectiles, uint64_t id_begin, uint64_t id_end, unsigned gens, unsigned stable_interval,
+                        lifeb200_hit* d_hits, size_t cap) {
+  const uint64_t n = id_end - id_begin;
+  if (int rc = ensure_tables(ctx, catalysts, n_catalysts, projectiles, n_projectiles)) return rc;
+  if (int rc = ensure_dense(ctx, n)) return rc;
+  uint64_t* dense = static_cast<uint64_t*>(ctx->d_dense);
+  const size_t words = (size_t)(n_catalysts + n_projectiles) * 2 * 64;
+  const uint64_t* d_cat = static_cast<const uint64_t*>(ctx->d_tabbuf);
+  const uint64_t* d_cz = d_cat + (size_t)n_catalysts * 64;
+  const uint64_t* d_pr = d_cz + (size_t)n_catalysts * 64;
+  const uint64_t* d_pz = d_pr + (size_t)n_projectiles * 64;
+  const uint32_t* d_packed = reinterpret_cast<const uint32_t*>(d_cat + words);
+  LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
+  // many generations: 4 placements per lane group in the row-class layout (enumerate_kernel_x), unless the
+  // caller pinned the lane grouping or another layout
+  const bool multi = ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kEnumerateMultiFrom));
+  if (multi) {
+    const uint64_t groups = (id_end - (id_begin & ~3ull) + 3) / 4;
+    LIFEB200_CUDA(cudaFuncSetAttribute(enumerate_kernel_x, cudaFuncAttributeMaxDynamicSharedMemorySize, kEnumXSmem));
+    enumerate_kernel_x<<<(unsigned)((groups * 8 + 127) / 128), 128, kEnumXSmem, ctx->stream>>>(
+        d_cz, d_pr, d_pz, d_packed, d_packed + (size_t)n_catalysts * 64 * 8, n_projectiles, id_begin, id_end, gens,
+        stable_interval, dense, ctx->d_counters + 1);
+  } else {
+    int lpp = match_lpp(ctx);
+    LIFEB200_DISPATCH_LPP_MIN4(lpp, (enumerate_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
+                                        d_cat, d_cz, d_pr, d_pz, n_projectiles, id_begin, id_end, gens, stable_interval, dense,
+                                        ctx->d_counters + 1)));
+  }
+  LIFEB200_LAUNCHED(ctx);
+  if (int rc = compact_hits(ctx, n, id_begin, d_hits, cap, ctx->d_counters + 0)) return rc;
+  LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
+                                ctx->stream));
+  LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+  return LIFEB200_OK;
+}
+
+int survey_to_device(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t seed, int dist, unsigned gens,
+                     lifeb200_hit* d_hits, size_t cap) {
+  if (int rc = ensure_dense(ctx, n)) return rc;
+  uint64_t* dense = static_cast<uint64_t*>(ctx->d_dense);
+  LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
+  // many generations: 4 soups per lane group in the row-class layout (life_multi.cuh), unless the caller
+  // pinned the lane grouping or the layout
+  const bool multi = ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kSurveyMultiFrom));
+  if (multi) {
+    const size_t groups = (n + 3) / 4;
+    survey_kernel_x<8><<<(unsigned)((groups * 8 + 127) / 128), 128, 0, ctx->stream>>>(
+        first_id, n, seed, dist, gens, dense, ctx->d_counters + 2, ctx->d_counters + 3);
+  } else {
+    int lpp = survey_lpp(ctx);
+    LIFEB200_DISPATCH_LPP_MIN4(lpp, (survey_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
+                                        first_id, n, seed, dist, gens, dense, ctx->d_counters + 2, ctx->d_counters + 3)));
+  }
+  LIFEB200_LAUNCHED(ctx);
+  if (int rc = compact_hits(ctx, n, first_id, d_hits, cap, ctx->d_counters + 0)) return rc;
+  LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
+                                ctx->stream));
+  LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+  return LIFEB200_OK;
+}
+
+// hits already sorted on the device: report the count, download what fits
+static int download_hits(lifeb200_ctx* ctx, const lifeb200_hit* d_hits, size_t cap, lifeb200_hit* hits, uint64_t* n_hits) {
+  const uint64_t found = ctx->h_counters[0];
+  if (n_hits) *n_hits = found;
+  const uint64_t k = std::min<uint64_t>(found, cap);
+  if (k && hits) {
+    LIFEB200_CUDA(cudaMemcpyAsync(hits, d_hits, k * sizeof(lifeb200_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+  }
+  if (found > cap) return set_error(LIFEB200_E_OVERFLOW, "hit buffer too small: %llu hits, capacity %llu",
+                                    (unsigned long long)found, (unsigned long long)cap);
+  return LIFEB200_OK;
+}
 
 }  // namespace lifeb200
 
@@ -485,52 +729,43 @@ int lifeb200_step_match_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const u
   if (n == 0) return LIFEB200_OK;
   if (!patterns || !targets || (!hits && cap)) return set_error(LIFEB200_E_ARG, "null pointer");
   if (!aligned16(patterns) || !aligned16(targets)) return set_error(LIFEB200_E_ARG, "pointers must be 16-byte aligned");
+  if (int rc = ensure_dense(ctx, n)) return rc;
+  uint64_t* dense = static_cast<uint64_t*>(ctx->d_dense);
   int lpp = match_lpp(ctx);
-  LIFEB200_DISPATCH_LPP(lpp, (step_match_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
-                                 patterns, targets, target_index, n, first_id, gens, stable_interval, hits, cap, n_hits)));
+  LIFEB200_DISPATCH_LPP_MIN4(lpp, (step_match_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
+                                      patterns, targets, target_index, n, gens, stable_interval, dense)));
   LIFEB200_LAUNCHED(ctx);
+  return compact_hits(ctx, n, first_id, hits, cap, n_hits);
+}
+
+static int enumerate_args(const uint64_t* catalysts, unsigned n_catalysts, const uint64_t* projectiles,
+                          unsigned n_projectiles, uint64_t id_begin, uint64_t* id_end, unsigned stable_interval,
+                          const lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* n_skipped, bool* empty) {
+  if (!catalysts || !projectiles || n_catalysts == 0 || n_projectiles == 0)
+    return set_error(LIFEB200_E_ARG, "empty catalyst / projectile table");
+  if (stable_interval == 0) return set_error(LIFEB200_E_ARG, "stable_interval must be >= 1");
+  const uint64_t total = (uint64_t)n_catalysts * n_projectiles * 4096ull;
+  if (*id_end > total) *id_end = total;
+  if (n_hits) *n_hits = 0;
+  if (n_skipped) *n_skipped = 0;
+  *empty = id_begin >= *id_end;
+  if (!*empty && !hits && cap) return set_error(LIFEB200_E_ARG, "null hits with non-zero capacity");
   return LIFEB200_OK;
 }
 
-// Hit records leave the device in atomic-reservation order; the caller gets them by id.  Ids are unique and lie
-// in [id_lo, id_lo + id_count): when a sizeable share of the range hit (a survey after few generations: most
-// soups are still active) one scatter through a slot table orders them in O(range + found) where std::sort
-// took 15 ms for 512 Ki records; sparse hit lists (the enumeration: thousands of hits in millions of ids) sort.
-static void order_hits(lifeb200_hit* hits, uint64_t found, uint64_t id_lo, uint64_t id_count) {
-  auto by_id = [](const lifeb200_hit& a, const lifeb200_hit& b) { return a.id < b.id; };
-  if (found < 2 || std::is_sorted(hits, hits + found, by_id)) return;
-  if (id_count < 0xFFFFFFFFull && found >= id_count / 16) {
-    std::vector<uint32_t> slot(id_count, 0xFFFFFFFFu);
-    bool ok = true;
-    for (uint64_t i = 0; i < found && ok; i++) {
-      const uint64_t k = hits[i].id - id_lo;
-      ok = k < id_count && slot[k] == 0xFFFFFFFFu;
-      if (ok) slot[k] = (uint32_t)i;
-    }
-    if (ok) {
-      const std::vector<lifeb200_hit> tmp(hits, hits + found);
-      uint64_t o = 0;
-      for (uint64_t k = 0; k < id_count; k++)
-        if (slot[k] != 0xFFFFFFFFu) hits[o++] = tmp[slot[k]];
-      return;
-    }
-  }
-  std::sort(hits, hits + found, by_id);
-}
-
-static int fetch_hits(lifeb200_ctx* ctx, lifeb200_hit* d_hits, size_t cap, lifeb200_hit* hits, uint64_t* n_hits,
-                      uint64_t id_lo, uint64_t id_count) {
-  // counters were copied to the pinned mirror and the stream synchronised by the caller
-  uint64_t found = ctx->h_counters[0];
-  if (n_hits) *n_hits = found;
-  if (found > cap) return set_error(LIFEB200_E_OVERFLOW, "hit buffer too small: %llu hits, capacity %llu",
-                                    (unsigned long long)found, (unsigned long long)cap);
-  if (found) {
-    LIFEB200_CUDA(cudaMemcpyAsync(hits, d_hits, found * sizeof(lifeb200_hit), cudaMemcpyDeviceToHost, ctx->stream));
-    LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
-    order_hits(hits, found, id_lo, id_count);
-  }
-  return LIFEB200_OK;
+int lifeb200_enumerate_collisions_dev(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts,
+                                      const uint64_t* projectiles, unsigned n_projectiles, uint64_t id_begin,
+                                      uint64_t id_end, unsigned gens, unsigned stable_interval, lifeb200_hit* d_hits,
+                                      size_t cap, uint64_t* n_hits, uint64_t* n_skipped) {
+  LIFEB200_CHECK_CTX(ctx);
+  bool empty = false;
+  if (int rc = enumerate_args(catalysts, n_catalysts, projectiles, n_projectiles, id_begin, &id_end, stable_interval,
+                              d_hits, cap, n_hits, n_skipped, &empty)) return rc;
+  if (empty) return LIFEB200_OK;
+  if (int rc = enumerate_to_device(ctx, catalysts, n_catalysts, projectiles, n_projectiles, id_begin, id_end, gens,
+                                   stable_interval, d_hits, cap)) return rc;
+  if (n_skipped) *n_skipped = ctx->h_counters[1];
+  return download_hits(ctx, d_hits, cap, nullptr, n_hits);
 }
 
 int lifeb200_enumerate_collisions(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts,
@@ -538,132 +773,52 @@ int lifeb200_enumerate_collisions(lifeb200_ctx* ctx, const uint64_t* catalysts, 
                                   uint64_t id_end, unsigned gens, unsigned stable_interval, lifeb200_hit* hits,
                                   size_t cap, uint64_t* n_hits, uint64_t* n_skipped) {
   LIFEB200_CHECK_CTX(ctx);
-  if (!catalysts || !projectiles || n_catalysts == 0 || n_projectiles == 0)
-    return set_error(LIFEB200_E_ARG, "empty catalyst / projectile table");
-  if (stable_interval == 0) return set_error(LIFEB200_E_ARG, "stable_interval must be >= 1");
-  const uint64_t total = (uint64_t)n_catalysts * n_projectiles * 4096ull;
-  if (id_end > total) id_end = total;
-  if (n_hits) *n_hits = 0;
-  if (n_skipped) *n_skipped = 0;
-  if (id_begin >= id_end) return LIFEB200_OK;
-  if (!hits && cap) return set_error(LIFEB200_E_ARG, "null hits with non-zero capacity");
-  const uint64_t n = id_end - id_begin;
-
-  // tables: cat | catZOI | proj | projZOI
-  const size_t words = (size_t)(n_catalysts + n_projectiles) * 2 * 64;
-  std::vector<uint64_t> tab(words);
-  uint64_t* h_cat = tab.data();
-  uint64_t* h_cz = h_cat + (size_t)n_catalysts * 64;
-  uint64_t* h_pr = h_cz + (size_t)n_catalysts * 64;
-  uint64_t* h_pz = h_pr + (size_t)n_projectiles * 64;
-  std::copy(catalysts, catalysts + (size_t)n_catalysts * 64, h_cat);
-  std::copy(projectiles, projectiles + (size_t)n_projectiles * 64, h_pr);
-  for (unsigned c = 0; c < n_catalysts; c++) host_zoi(h_cat + (size_t)c * 64, h_cz + (size_t)c * 64);
-  for (unsigned g = 0; g < n_projectiles; g++) host_zoi(h_pr + (size_t)g * 64, h_pz + (size_t)g * 64);
-
-  // many generations: 4 placements per lane group in the row-class layout (enumerate_kernel_x), unless the
-  // caller pinned the lane grouping or another layout.  Its target planes are packed here: every cell of
-  // wanted (= catalyst) and mask (= its ZOI) replicated into the four pattern bits of register (column, k).
-  const bool multi = ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kEnumerateMultiFrom));
-  std::vector<uint32_t> packed;
-  if (multi) {
-    packed.resize((size_t)n_catalysts * 64 * 8 * 2);
-    uint32_t* pk_w = packed.data();
-    uint32_t* pk_m = pk_w + (size_t)n_catalysts * 64 * 8;
-    for (size_t ci = 0; ci < (size_t)n_catalysts * 64; ci++)
-      for (int k = 0; k < 8; k++) {
-        uint32_t w = 0, m = 0;
-        for (int j = 0; j < 8; j++) {
-          if (h_cat[ci] >> (8 * j + k) & 1) w |= 0xFu << (4 * j);
-          if (h_cz[ci] >> (8 * j + k) & 1) m |= 0xFu << (4 * j);
-        }
-        pk_w[ci * 8 + k] = w;
-        pk_m[ci * 8 + k] = m;
-      }
-  }
-
-  uint64_t* d_tab = nullptr;
-  uint32_t* d_packed = nullptr;
-  lifeb200_hit* d_hits = nullptr;
+  bool empty = false;
+  if (int rc = enumerate_args(catalysts, n_catalysts, projectiles, n_projectiles, id_begin, &id_end, stable_interval,
+                              hits, cap, n_hits, n_skipped, &empty)) return rc;
+  if (empty) return LIFEB200_OK;
   // context-owned scratch (ctx.h): no allocation after the first call of a given size
-  if (int rc0 = ensure_scratch(ctx->d_tabbuf, ctx->tabbuf_cap, words * 8 + packed.size() * 4)) return rc0;
-  d_tab = static_cast<uint64_t*>(ctx->d_tabbuf);
-  d_packed = reinterpret_cast<uint32_t*>(d_tab + words);
-  if (cap) {
-    if (int rc0 = ensure_scratch(ctx->d_hitbuf, ctx->hitbuf_cap, cap * sizeof(lifeb200_hit))) return rc0;
-    d_hits = static_cast<lifeb200_hit*>(ctx->d_hitbuf);
-  }
-  int rc = LIFEB200_OK;
-  auto body = [&]() -> int {
-    LIFEB200_CUDA(cudaMemcpyAsync(d_tab, tab.data(), words * 8, cudaMemcpyHostToDevice, ctx->stream));
-    LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
-    const uint64_t* d_cat = d_tab;
-    const uint64_t* d_cz = d_cat + (size_t)n_catalysts * 64;
-    const uint64_t* d_pr = d_cz + (size_t)n_catalysts * 64;
-    const uint64_t* d_pz = d_pr + (size_t)n_projectiles * 64;
-    if (multi) {
-      LIFEB200_CUDA(cudaMemcpyAsync(d_packed, packed.data(), packed.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
-      const uint64_t groups = (id_end - (id_begin & ~3ull) + 3) / 4;
-      LIFEB200_CUDA(cudaFuncSetAttribute(enumerate_kernel_x, cudaFuncAttributeMaxDynamicSharedMemorySize, kEnumXSmem));
-      enumerate_kernel_x<<<(unsigned)((groups * 8 + 127) / 128), 128, kEnumXSmem, ctx->stream>>>(
-          d_cz, d_pr, d_pz, d_packed, d_packed + (size_t)n_catalysts * 64 * 8, n_projectiles, id_begin, id_end, gens,
-          stable_interval, d_hits, cap, ctx->d_counters + 0, ctx->d_counters + 1);
-    } else {
-      int lpp = match_lpp(ctx);
-      LIFEB200_DISPATCH_LPP(lpp, (enumerate_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
-                                     d_cat, d_cz, d_pr, d_pz, n_projectiles, id_begin, id_end, gens, stable_interval, d_hits,
-                                     cap, ctx->d_counters + 0, ctx->d_counters + 1)));
-    }
-    LIFEB200_LAUNCHED(ctx);
-    LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 4 * sizeof(unsigned long long),
-                                  cudaMemcpyDeviceToHost, ctx->stream));
-    LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (n_skipped) *n_skipped = ctx->h_counters[1];
-    return fetch_hits(ctx, d_hits, cap, hits, n_hits, id_begin, id_end - id_begin);
-  };
-  rc = body();
-  return rc;
+  if (int rc = ensure_scratch(ctx->d_hitbuf, ctx->hitbuf_cap, std::max<size_t>(cap, 1) * sizeof(lifeb200_hit))) return rc;
+  lifeb200_hit* d_hits = static_cast<lifeb200_hit*>(ctx->d_hitbuf);
+  if (int rc = enumerate_to_device(ctx, catalysts, n_catalysts, projectiles, n_projectiles, id_begin, id_end, gens,
+                                   stable_interval, d_hits, cap)) return rc;
+  if (n_skipped) *n_skipped = ctx->h_counters[1];
+  return download_hits(ctx, d_hits, cap, hits, n_hits);
 }
 
-int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t seed, int dist, unsigned gens,
-                         lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* pop_sum, uint64_t* hash_xor) {
-  LIFEB200_CHECK_CTX(ctx);
+static int survey_args(uint64_t* n_hits, uint64_t* pop_sum, uint64_t* hash_xor, int dist, unsigned gens) {
   if (gens < 2) return set_error(LIFEB200_E_ARG, "survey needs gens >= 2");
   if (dist != 0 && dist != 1) return set_error(LIFEB200_E_ARG, "dist must be 0 or 1");
   if (n_hits) *n_hits = 0;
   if (pop_sum) *pop_sum = 0;
   if (hash_xor) *hash_xor = 0;
+  return LIFEB200_OK;
+}
+
+int lifeb200_soup_survey_dev(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t seed, int dist, unsigned gens,
+                             lifeb200_hit* d_hits, size_t cap, uint64_t* n_hits, uint64_t* pop_sum, uint64_t* hash_xor) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (int rc = survey_args(n_hits, pop_sum, hash_xor, dist, gens)) return rc;
+  if (n == 0) return LIFEB200_OK;
+  if (!d_hits && cap) return set_error(LIFEB200_E_ARG, "null hits with non-zero capacity");
+  if (int rc = survey_to_device(ctx, first_id, n, seed, dist, gens, d_hits, cap)) return rc;
+  if (pop_sum) *pop_sum = ctx->h_counters[2];
+  if (hash_xor) *hash_xor = ctx->h_counters[3];
+  return download_hits(ctx, d_hits, cap, nullptr, n_hits);
+}
+
+int lifeb200_soup_survey(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t seed, int dist, unsigned gens,
+                         lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* pop_sum, uint64_t* hash_xor) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (int rc = survey_args(n_hits, pop_sum, hash_xor, dist, gens)) return rc;
   if (n == 0) return LIFEB200_OK;
   if (!hits && cap) return set_error(LIFEB200_E_ARG, "null hits with non-zero capacity");
-  lifeb200_hit* d_hits = nullptr;
-  if (cap) {
-    if (int rc0 = ensure_scratch(ctx->d_hitbuf, ctx->hitbuf_cap, cap * sizeof(lifeb200_hit))) return rc0;
-    d_hits = static_cast<lifeb200_hit*>(ctx->d_hitbuf);
-  }
-  auto body = [&]() -> int {
-    LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
-    // many generations: 4 soups per lane group in the row-class layout (life_multi.cuh), unless the caller
-    // pinned the lane grouping or the layout
-    const bool multi = ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kSurveyMultiFrom));
-    if (multi) {
-      const size_t groups = (n + 3) / 4;
-      survey_kernel_x<8><<<(unsigned)((groups * 8 + 127) / 128), 128, 0, ctx->stream>>>(
-          first_id, n, seed, dist, gens, d_hits, cap, ctx->d_counters + 0, ctx->d_counters + 2, ctx->d_counters + 3);
-    } else {
-      int lpp = survey_lpp(ctx);
-      LIFEB200_DISPATCH_LPP(lpp, (survey_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
-                                     first_id, n, seed, dist, gens, d_hits, cap, ctx->d_counters + 0, ctx->d_counters + 2,
-                                     ctx->d_counters + 3)));
-    }
-    LIFEB200_LAUNCHED(ctx);
-    LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 4 * sizeof(unsigned long long),
-                                  cudaMemcpyDeviceToHost, ctx->stream));
-    LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (pop_sum) *pop_sum = ctx->h_counters[2];
-    if (hash_xor) *hash_xor = ctx->h_counters[3];
-    return fetch_hits(ctx, d_hits, cap, hits, n_hits, first_id, n);
-  };
-  return body();
+  if (int rc = ensure_scratch(ctx->d_hitbuf, ctx->hitbuf_cap, std::max<size_t>(cap, 1) * sizeof(lifeb200_hit))) return rc;
+  lifeb200_hit* d_hits = static_cast<lifeb200_hit*>(ctx->d_hitbuf);
+  if (int rc = survey_to_device(ctx, first_id, n, seed, dist, gens, d_hits, cap)) return rc;
+  if (pop_sum) *pop_sum = ctx->h_counters[2];
+  if (hash_xor) *hash_xor = ctx->h_counters[3];
+  return download_hits(ctx, d_hits, cap, hits, n_hits);
 }
 
 int lifeb200_fold_dev(lifeb200_ctx* ctx, const uint64_t* patterns, size_t n, uint64_t first_id, uint64_t* pop_sum,

@@ -195,7 +195,7 @@ int lifeb200_weld_step_batch_dev(lifeb200_ctx* ctx, uint64_t* records, size_t n,
   if (n == 0 || gens == 0) return LIFEB200_OK;
   if (!records || !aligned16(records)) return set_error(LIFEB200_E_ARG, "bad record pointer");
   int lpp = std::max(8, effective_lpp(ctx));  // 8 tiles live: keep W <= 8
-  LIFEB200_DISPATCH_LPP(lpp, (weld_step_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, ctx->stream>>>(records, n, gens)));
+  LIFEB200_DISPATCH_LPP_MIN4(lpp, (weld_step_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, ctx->stream>>>(records, n, gens)));
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }
@@ -205,7 +205,7 @@ int lifeb200_interaction_counts_dev(lifeb200_ctx* ctx, const uint64_t* in, uint6
   if (n == 0) return LIFEB200_OK;
   if (!in || !planes || !aligned16(in) || !aligned16(planes)) return set_error(LIFEB200_E_ARG, "null or misaligned pointer");
   int lpp = ctx->lpp ? std::max(8, ctx->lpp) : 32;
-  LIFEB200_DISPATCH_LPP(lpp, (interaction_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, ctx->stream>>>(in, planes, n)));
+  LIFEB200_DISPATCH_LPP_MIN4(lpp, (interaction_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, ctx->stream>>>(in, planes, n)));
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }

@@ -182,7 +182,7 @@ int launch_ncount(lifeb200_ctx* ctx, cudaStream_t st, const uint64_t* in, uint64
   // 5 tiles in registers: keep W <= 16.  A single pass with 2 KiB out per pattern: a warp per pattern makes every
   // plane store one contiguous 512-byte request (see interaction_kernel, csrc/next.cu)
   int lpp = ctx->lpp ? std::max(4, ctx->lpp) : 32;
-  LIFEB200_DISPATCH_LPP(lpp, (ncount_kernel<LPP><<<grid_for(n, LPP), kBlock, 0, st>>>(in, planes, n)));
+  LIFEB200_DISPATCH_LPP_MIN4(lpp, (ncount_kernel<LPP><<<grid_for(n, LPP), kBlock, 0, st>>>(in, planes, n)));
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }

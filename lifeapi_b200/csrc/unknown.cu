@@ -222,7 +222,7 @@ int lifeb200_history_step_batch_dev(lifeb200_ctx* ctx, uint64_t* records, size_t
   if (n == 0 || gens == 0) return LIFEB200_OK;
   if (!records || !aligned16(records)) return set_error(LIFEB200_E_ARG, "bad record pointer");
   int lpp = std::max(4, effective_lpp(ctx));
-  LIFEB200_DISPATCH_LPP(lpp, (history_step_kernel<LPP><<<grid_u(n, LPP), kBlockU, 0, ctx->stream>>>(records, n, gens)));
+  LIFEB200_DISPATCH_LPP_MIN4(lpp, (history_step_kernel<LPP><<<grid_u(n, LPP), kBlockU, 0, ctx->stream>>>(records, n, gens)));
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }
