@@ -20,7 +20,7 @@ LIB = os.path.join(LIBDIR, "liblifeapi_b200.so")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-shared", "-t", "0",
+    "-Xcompiler", "-fPIC", "-shared", "-t", "0", "-ldl",
 ]
 
 

