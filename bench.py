@@ -32,11 +32,40 @@ SEED = 0x4C696665415049
 N_SOUPS = 1 << 20
 GENS = 1024
 INSTR_PER_CELL = 12.0 / 32.0  # algorithmic 2 SHF + 10 LOP3 per 32 cells per generation
-EXECUTED_INSTR_PER_CELL = 7.75 / 32.0  # what step_kernel_x<8> issues: 4 patterns bit-interleaved per register + pair-shared select
-# dram bytes of one 1 Mi-soup x 1024-generation step_kernel launch from the committed ncu capture
-# (profiles/r01z_step_kernel_x8_raw.csv: dram__bytes_read.sum 547.10 MB + dram__bytes_write.sum 489.27 MB;
-# the write side is below 512 MiB because the tail of the output is still in the 126 MB L2 at kernel end)
-STEP_KERNEL_DRAM_BYTES_PER_LAUNCH = 547099392 + 489269504
+# What step_kernel_x<8> EXECUTES per 32 cells and generation is read from the committed SASS histogram of the shipped
+# library (profiles/r02_sass_mix.json, made by tools/sass_mix.py from `cuobjdump -sass`); 7.75 is the fallback.
+# DRAM traffic of one launch is read from the committed `ncu --set full` capture of this launch shape.
+SASS_MIX_FILES = ["profiles/r02_sass_mix.json"]
+NCU_RAW_FILES = ["profiles/r02_step_kernel_x8_raw.csv", "profiles/r01z_step_kernel_x8_raw.csv"]
+
+
+def executed_instr_per_32_cells(kernel="step_kernel_x<8>"):
+    for rel in SASS_MIX_FILES:
+        try:
+            k = json.load(open(os.path.join(ROOT, rel)))["kernels"][kernel]
+            g = k["generation_loop"]
+            return float(k["alu_instr_per_32_cells"]), {"file": rel, "loop_instructions": g["instructions"], "pipes": g["pipes"],
+                                                         "ops": {o: c for o, c in list(g["ops"].items())[:6]}}
+        except Exception:  # noqa: BLE001
+            continue
+    return 7.75, {"file": None, "note": "fallback constant (no committed SASS histogram found)"}
+
+
+def ncu_dram_traffic(kernel_substr="step_kernel_x<8>", grid="(16384, 1, 1)"):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the committed capture of the same launch shape, or None."""
+    import csv
+    for rel in NCU_RAW_FILES:
+        try:
+            rows = list(csv.reader(open(os.path.join(ROOT, rel))))
+            hdr = rows[0]
+            ik, ig = hdr.index("Kernel Name"), hdr.index("Grid Size")
+            ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+            for r in rows[2:]:
+                if kernel_substr in r[ik] and r[ig] == grid:
+                    return int(float(r[ir])) + int(float(r[iw])), rel
+        except Exception:  # noqa: BLE001
+            continue
+    return None, None
 METRIC = "cell_updates_per_sec"
 UNIT = "Gcell/s"
 
@@ -54,6 +83,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the config 3/4/5 side measurements")
+    ap.add_argument("--no-survey", action="store_true", help="skip the config 5 survey + NCCL gather leg")
+    ap.add_argument("--survey-soups", type=int, default=1 << 24, help="config 5 batch (whole job, every N)")
     return ap.parse_args()
 
 
@@ -74,28 +105,52 @@ def load_cpu_checker():
     return ref if ref is not None else Port()
 
 
-def cpu_time_sample(chk, soups, gens, threads):
+def cpu_time_sample(chk, soups, gens, threads, keep=None):
     t0 = time.perf_counter()
-    chk.step_batch(soups, gens, threads)
-    return time.perf_counter() - t0
+    out = chk.step_batch(soups, gens, threads)
+    dt = time.perf_counter() - t0
+    if keep is not None:
+        keep.append(out)
+    return dt
 
 
-def cpu_baseline(gens, target_s=10.0):
+def cpu_baseline(gens, first_id=0, n_max=1 << 18, target_s=10.0):
+    """Times the reference on a bounded sample of the workload's soups AND returns what it computed, so that the
+    same run can compare it with the GPU's rows (the bit-exact verdict of BASELINE.md's same-run rule)."""
     from oracle.loader import Port
     chk = load_cpu_checker()
     threads = chk.threads()
     port = Port()
     cal_n = 256 * max(1, threads)
-    soups = port.soup(0, cal_n, SEED, 0)
+    soups = port.soup(first_id, cal_n, SEED, 0)
     dt = cpu_time_sample(chk, soups, gens, threads)
     rate = cal_n / max(dt, 1e-6)
-    n = int(min(max(rate * target_s, cal_n), 1 << 18))
-    soups = port.soup(0, n, SEED, 0)
-    dt = cpu_time_sample(chk, soups, gens, threads)
+    n = int(min(max(rate * target_s, cal_n), n_max))
+    soups = port.soup(first_id, n, SEED, 0)
+    keep = []
+    dt = cpu_time_sample(chk, soups, gens, threads, keep)
     cells = n * 4096.0 * gens
     return {"value": cells / dt / 1e9, "unit": UNIT, "cores": threads, "kind": chk.kind,
             "sample": f"{n} of the same seeded soups x {gens} generations, contiguous chunks over {threads} threads, "
-                      f"{dt:.1f} s wall" + (f", isa {chk.isa()}" if hasattr(chk, "isa") else "")}
+                      f"{dt:.1f} s wall" + (f", isa {chk.isa()}, built -march=x86-64-v4/v3/v2 (oracle/Makefile)" if hasattr(chk, "isa") else "")}, keep[0]
+
+
+def parity_against_cpu(eng, d_out, first_id, n, gens, cpu_rows=None, sample=4096):
+    """Bit-exact verdict: the GPU's output rows against the reference's Step(n) of the same soups."""
+    from oracle.loader import Port
+    if cpu_rows is None:
+        chk = load_cpu_checker()
+        m = min(sample, n)
+        cpu_rows = chk.step_batch(Port().soup(first_id, m, SEED, 0), gens, 0)
+        kind = chk.kind
+    else:
+        kind = load_cpu_checker().kind
+    m = min(len(cpu_rows), n)
+    got = np.empty((m, 64), dtype=np.uint64)
+    eng.d2h(got, d_out)
+    eng.sync()
+    return {"checked": int(m), "equal": bool((got == np.asarray(cpu_rows)[:m]).all()), "vs": kind,
+            "what": f"every word of the first {m} output patterns of this rank against LifeState::Step({gens}) on the host"}
 
 
 def run_reference_arm(args, rank, world):
@@ -224,7 +279,7 @@ def main():
     import torch
     import torch.distributed as dist
 
-    from lifeapi_b200 import HIT_DTYPE, Engine, gather_hits
+    from lifeapi_b200 import HIT_DTYPE, Engine
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU fallback (use --impl reference)")
@@ -290,36 +345,60 @@ def main():
     value = cells_per_step_all * args.steps / (ms * 1e-3) / 1e9
     kernel_ms = ms / args.steps
 
-    # ---- counters / checksum gathered over NCCL (the path's only collective) --------
-    pop_sum, hash_xor = eng.fold_dev(d_out, n, first_id)
-    survey_gather = None
+    # ---- counters / checksum of the headline batch ---------------------------------------------------------
+    local_fold = eng.fold_dev(d_out, n, first_id)  # this rank's (pop_sum, hash_xor) of the resident result
+    pop_sum, hash_xor = local_fold
     if distributed:
-        _, sums, xors = gather_hits(np.zeros(0, dtype=HIT_DTYPE), [pop_sum, hash_xor], device=dev)
-        pop_sum, hash_xor = sums[0], xors[1]
-        # config 5 shape: each rank surveys its shard of one global id range on device, then the hit
-        # lists and counters are gathered over NCCL (the path's only collective)
-        from lifeapi_b200 import shard_range
-        # 2 Mi soups per rank x 4096 generations: at 8 ranks this IS BASELINE config 5 (16 Mi soups), below that the
-        # same per-rank share of it (weak scaling)
-        total5, gens5 = world << 21, 4096
-        lo, hi = shard_range(total5, rank, world)
-        # one untimed gather of a comparable size first: NCCL sets its channels up on the first collective of a shape
-        gather_hits(np.zeros(1 << 15, dtype=HIT_DTYPE), [0, 0], device=dev)
-        barrier()
-        t0 = time.perf_counter()
-        hits5, ps5, hx5 = eng.soup_survey(lo, hi - lo, SEED, 0, gens5, hi - lo)
-        t_local = time.perf_counter() - t0
-        merged, sums5, xors5 = gather_hits(hits5, [ps5, hx5], device=dev)
-        torch.cuda.synchronize()
-        t_total = max_over_ranks(time.perf_counter() - t0)   # survey + gather, slowest rank
-        t_local = max_over_ranks(t_local)
-        t_gather = max(t_total - t_local, 0.0)                # what the gather adds after the slowest survey
-        survey_gather = {"workload": f"config5: {total5} on-device soups x {gens5} gens sharded by id over {world} ranks, hit lists gathered over NCCL",
-                         "active_hits_total": int(len(merged)), "hits_sorted_unique": bool((np.diff(merged["id"].astype(np.int64)) > 0).all()),
-                         "pop_sum": int(sums5[0]), "hash_xor": f"{int(xors5[1]):016x}", "survey_s": t_local,
-                         "gather_s": t_gather, "gather_bytes": int(len(merged)) * 16,
-                         "total_s": t_total,
-                         "value": total5 * 4096.0 * gens5 / t_total / 1e9, "unit": UNIT}
+        t = torch.tensor([pop_sum & 0x7FFFFFFFFFFFFFFF, pop_sum >> 63, hash_xor & 0x7FFFFFFFFFFFFFFF, hash_xor >> 63],
+                         dtype=torch.int64, device=dev)
+        ts = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(ts, t)
+        pop_sum = sum(int(x[0]) | (int(x[1]) << 63) for x in ts) & 0xFFFFFFFFFFFFFFFF
+        hash_xor = 0
+        for x in ts:
+            hash_xor ^= int(x[2]) | (int(x[3]) << 63)
+
+    # ---- BASELINE config 5: ONE batch of 16 Mi on-device soups x 4096 generations, sharded by id over the ranks
+    # (strong scaling: the same batch at every N), hit lists and counters gathered over NCCL by the C library itself
+    # (lifeb200_multi_soup_survey, csrc/multi.cu; torch only hands the 128-byte NCCL unique id to the ranks)
+    survey_gather = None
+    if not args.no_survey:
+        from lifeapi_b200 import MultiEngine
+        total5, gens5 = args.survey_soups, 4096
+        uid = [MultiEngine.unique_id() if (distributed and rank == 0) else None]
+        if distributed:
+            dist.broadcast_object_list(uid, src=0)
+        group = MultiEngine(device=local_rank, rank=rank, world=world, unique_id=uid[0])
+        try:
+            cap5 = total5
+            h_hits = np.zeros(cap5 if rank == 0 else 1, dtype=HIT_DTYPE)
+            group.soup_survey(0, min(total5, world << 12), SEED, 0, 16, cap5, hits=h_hits)  # untimed: NCCL channel set-up, scratch
+            barrier()
+            t0 = time.perf_counter()
+            merged, ps5, hx5 = group.soup_survey(0, total5, SEED, 0, gens5, cap5, hits=h_hits)
+            t_total = max_over_ranks(time.perf_counter() - t0)   # survey + gather + download, slowest rank
+            gather_ms = max_over_ranks(group.last_gather_ms())
+            cross = None
+            if rank == 0:
+                # multi-rank parity: rank 0 re-surveys 64 Ki ids that belong to the LAST rank (and, at N = 1, to itself)
+                # on its own GPU and compares them with the records the gather delivered for that range
+                lo = group.shard(0, total5, world - 1)[0]
+                m = min(1 << 16, total5 - lo)
+                own, _, _ = eng.soup_survey(lo, m, SEED, 0, gens5, m)
+                sel = (merged["id"] >= lo) & (merged["id"] < lo + m)
+                cross = {"range": [int(lo), int(lo + m)], "owner_rank": world - 1, "records": int(sel.sum()),
+                         "equal": bool(own.tobytes() == merged[sel].tobytes())}
+            survey_gather = {"workload": f"config5: ONE batch of {total5} on-device soups x {gens5} gens sharded by id over {world} rank(s) "
+                                         f"(strong scaling), hit lists gathered over NCCL inside the C library",
+                             "api": "lifeb200_multi_create_rank + lifeb200_multi_soup_survey", "nccl_version": group.info()["nccl_version"],
+                             "active_hits_total": int(len(merged)) if rank == 0 else None,
+                             "hits_sorted_unique": bool((np.diff(merged["id"].astype(np.int64)) > 0).all()) if rank == 0 else None,
+                             "pop_sum": int(ps5), "hash_xor": f"{int(hx5):016x}", "total_s": t_total, "gather_ms_device": gather_ms,
+                             "gather_bytes": int(len(merged)) * 16 if rank == 0 else None,
+                             "value": total5 * 4096.0 * gens5 / t_total / 1e9, "unit": UNIT,
+                             "cross_rank_parity": cross}
+        finally:
+            group.close()
 
     # ---- HBM-bound companion: one generation per launch (load/store phases dominate) -----------
     for _ in range(3):
@@ -361,7 +440,13 @@ def main():
                "d2h_bytes_per_step": nbytes * world, "ms_per_step": dt / args.steps * 1e3,
                "ms_per_step_by_rank": [round(x / args.steps * 1e3, 3) for x in by_rank],
                "host_memory": "pinned (lifeb200_host_alloc)", "host_affinity": host_affinity, "api": "lifeb200_step_batch_host",
-               "matches_resident_path": bool(distributed or chk == (pop_sum, hash_xor))}
+               "matches_resident_path": None}
+        ok = 1 if chk == local_fold else 0   # per rank: the host path's output folds to this rank's resident checksum
+        if distributed:
+            t = torch.tensor([ok], dtype=torch.int64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            ok = int(t.item())
+        e2e["matches_resident_path"] = bool(ok)
         eng.host_free(h_in)
         eng.host_free(h_out)
 
@@ -374,26 +459,43 @@ def main():
     hbm_src = "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
 
     per_gpu_cells_s = n * 4096.0 * gens / (kernel_ms * 1e-3)
-    achieved = per_gpu_cells_s * INSTR_PER_CELL
-    roofline = {"bound": "int_pipe", "achieved": achieved / 1e12, "peak": p_int / 1e12, "unit": "T lane-instr/s (LOP3+SHF)",
-                "frac": achieved / p_int,
-                "traffic": STEP_KERNEL_DRAM_BYTES_PER_LAUNCH if (n, gens) == (N_SOUPS, GENS) else None,
-                "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of this launch shape "
-                                  "(profiles/, see DESIGN.md 6); algorithmic = 2 x 512 B x soups",
+    layout8 = (args.layout in (0, 8)) and args.lpp == 0 and gens >= 20
+    exec_per32, exec_src = executed_instr_per_32_cells("step_kernel_x<8>") if layout8 else (None, {"note": "non-default kernel"})
+    traffic, traffic_file = ncu_dram_traffic() if (n, gens) == (N_SOUPS, GENS) and layout8 else (None, None)
+    achieved_exec = per_gpu_cells_s * (exec_per32 / 32.0) if exec_per32 else None
+    achieved_alg = per_gpu_cells_s * INSTR_PER_CELL
+    roofline = {"bound": "int_pipe", "unit": "T lane-instr/s (LOP3+SHF)", "peak": p_int / 1e12,
+                # achieved / frac: integer-pipe instructions the kernel EXECUTES (SASS histogram of the shipped .so) per
+                # second against the LOP3 rate measured in this run -- a fraction of the pipe, <= 1 by construction
+                "achieved": (achieved_exec or achieved_alg) / 1e12, "frac": (achieved_exec or achieved_alg) / p_int,
+                "executed_instr_per_32_cells": exec_per32, "frac_executed": achieved_exec / p_int if achieved_exec else None,
+                "executed_source": exec_src,
+                # SURVEY 8(d)'s algorithmic figure (the literal two-full-adder form: 2 SHF + 10 LOP3 per 32 cells): what a
+                # kernel issuing that form would need; above 1 because the shipped circuit is cheaper, not because work is skipped
+                "algorithmic_equiv": {"instr_per_32_cells": 12.0, "achieved": achieved_alg / 1e12, "frac": achieved_alg / p_int,
+                                      "what": "cells/s x 0.375 instr per cell-update (SURVEY 8d) / measured LOP3 peak"},
+                "traffic": traffic,
+                "traffic_source": f"dram__bytes_read.sum + dram__bytes_write.sum of this launch shape, read from {traffic_file} "
+                                  "(ncu --set full)" if traffic_file else None,
                 "algorithmic_bytes": 2 * nbytes,
-                "kernel": "step_kernel_x<8>", "kernel_ms": kernel_ms,
-                "algorithmic": "12 int-pipe instr per 32 cells per generation = 0.375 instr/cell-update (SURVEY 8d)",
-                "executed": "7.75 int-pipe instr per 32 cells per generation (0.25 SHF + 7.5 LOP3: rows by class mod 8, 4 patterns bit-interleaved per register, pair-shared select)",
-                "pipe_utilisation": per_gpu_cells_s * EXECUTED_INSTR_PER_CELL / p_int,
+                "kernel": "step_kernel_x<8>" if layout8 else "step_kernel", "kernel_ms": kernel_ms,
                 "peak_source": f"LOP3 microbenchmark in this run (lifeb200_measure_int_peak): {p_int / 1e12:.2f} T/s = "
                                f"{info['sm_count']} SMs x 64 lanes x {mhz_eff:.0f} MHz effective",
                 "hbm": {"bound": "hbm", "achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak,
                         "what": "same kernel at 1 generation per launch (512 B in + 512 B out per pattern)",
                         "ms": ms1, "peak_source": hbm_src, "traffic": None}}
 
-    cpu = None
+    # ---- CPU baseline (rank 0 at N = 1) and the bit-exact verdict of the same run (every rank) ----------------
+    cpu, cpu_rows = None, None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = cpu_baseline(gens)
+        cpu, cpu_rows = cpu_baseline(gens, first_id, n_max=min(1 << 18, n))
+    eng.step_batch_dev(d_in, d_out, n, gens)  # d_out was reused by the e2e check: recompute the resident result
+    parity = parity_against_cpu(eng, d_out, first_id, n, gens, cpu_rows)
+    if distributed:
+        t = torch.tensor([1 if parity["equal"] else 0, parity["checked"]], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        parity["equal"] = bool(int(t[0].item()))
+        parity["what"] += f"; every one of the {world} ranks checked its own first {parity['checked']} and all agree"
     extras = None
     if world == 1 and not args.no_extras:
         from bench_extras import run_extras
@@ -403,7 +505,7 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": kernel_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
                 "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e,
-                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "other_configs": extras, "survey_gather": survey_gather,
+                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "other_configs": extras, "survey_gather": survey_gather,
                 "checksum": {"pop_sum": int(pop_sum), "hash_xor": f"{int(hash_xor):016x}"},
                 "lanes_per_pattern": args.lpp or "default", "step_layout": args.layout or "auto", "device": {"sms": info["sm_count"], "cc": list(info["cc"])}}
         _emit(line)

@@ -54,7 +54,7 @@ def _cpu_ref():
 def config3_unknown_step(eng, p_int):
     """256 Ki partial patterns x 16 three-valued generations (bitslicing/unknown_step.hpp)."""
     n, gens = 1 << 18, 16
-    d_s, d_u, d_t = eng.malloc(n * 512), eng.malloc(n * 512), eng.malloc(n * 512)
+    d_s, d_u, d_t, d_o = eng.malloc(n * 512), eng.malloc(n * 512), eng.malloc(n * 512), eng.malloc(n * 512)
     try:
         # state = soup masked to the centred 32x32 box; unknown = AND of three other soups (density 1/8) in the box
         eng.soup_dev(d_s, 0, n, SEED, 0)
@@ -68,14 +68,13 @@ def config3_unknown_step(eng, p_int):
         eng.h2d(d_s, st)
         eng.h2d(d_u, unk)
         eng.sync()
-        d_o = eng.malloc(n * 512)
         ms = _time(eng, lambda: eng.unknown_step_batch_dev(d_s, d_u, d_t, d_o, n, gens))
         eng.set_three_valued_path(1)
         ms_lit = _time(eng, lambda: eng.unknown_step_batch_dev(d_s, d_u, d_t, d_o, n, gens))
         eng.set_three_valued_path(0)
         long_gens = 256
         ms_long = _time(eng, lambda: eng.unknown_step_batch_dev(d_s, d_u, d_t, d_o, n, long_gens))
-        eng.free(d_o)
+        d_o2 = d_o
         cells = n * 4096.0 * gens
         out = {"workload": f"config3: {n} partial patterns x {gens} three-valued generations", "ms": ms,
                "value": cells / (ms * 1e-3) / 1e9, "unit": "Gcell/s",
@@ -91,15 +90,21 @@ def config3_unknown_step(eng, p_int):
                             "pipe_utilisation": n * 4096.0 * long_gens * (24.0 / 32.0) / (ms_long * 1e-3) / p_int}}
         ref = _cpu_ref()
         if ref is not None:
-            m = 1 << 16
             t0 = time.perf_counter()
-            ref.unknown_step_batch(st[:m], unk[:m], gens, 0)
+            want_s, want_u = ref.unknown_step_batch(st, unk, gens, 0)
             dt = time.perf_counter() - t0
-            out["cpu_baseline"] = {"value": m * 4096.0 * gens / dt / 1e9, "unit": "Gcell/s", "cores": ref.threads(),
-                                   "kind": "reference", "sample": f"{m} patterns x {gens} gens, {dt:.2f} s"}
+            out["cpu_baseline"] = {"value": n * 4096.0 * gens / dt / 1e9, "unit": "Gcell/s", "cores": ref.threads(),
+                                   "kind": "reference", "sample": f"all {n} patterns x {gens} gens, {dt:.2f} s, {ref.threads()} threads"}
+            eng.unknown_step_batch_dev(d_s, d_u, d_t, d_o2, n, gens)
+            got_s, got_u = np.empty_like(st), np.empty_like(unk)
+            eng.d2h(got_s, d_t)
+            eng.d2h(got_u, d_o2)
+            eng.sync()
+            out["parity"] = {"checked": int(n), "equal": bool((got_s == want_s).all() and (got_u == want_u).all()), "vs": "reference",
+                             "what": "both planes of every pattern against NeighbourCount + the committed unknown_step.hpp text"}
         return out
     finally:
-        for p in (d_s, d_u, d_t):
+        for p in (d_s, d_u, d_t, d_o):
             eng.free(p)
 
 
@@ -125,15 +130,29 @@ def config4_enumeration(eng, p_int):
            "skipped_overlapping": int(skipped), "timing": "wall clock around the host-facing C-ABI call (tables up, hits down, sorted)"}
     ref = _cpu_ref()
     if ref is not None:
-        m = 1 << 14
-        t0 = time.perf_counter()
-        ids, ff, rec, sk = ref.enumerate(cats, gliders, 0, m, gens, interval, m)
-        dt_cpu = time.perf_counter() - t0
-        sub = hits[hits["id"] < m]
-        out["cpu_baseline"] = {"placements_per_s": m / dt_cpu, "cores": 1, "kind": "reference",
-                               "sample": f"first {m} placement ids, {dt_cpu:.2f} s, 1 thread",
-                               "hits_equal_on_sample": bool(len(sub) == len(ids) and (sub["id"] == ids).all()
-                                                            and (sub["g_first_false"] == ff).all() and (sub["g_recovered"] == rec).all())}
+        # 1/16 of the id space, spread over all 32 catalysts: for every catalyst the 2 glider variants c % 16 and
+        # (c + 8) % 16 + 16, all 4096 offsets of each, the reference's own loop on every host thread
+        per_cat = 32 * 4096
+        ranges = []
+        for c in range(32):
+            for g in (c % 16, (c + 8) % 16 + 16):
+                lo = c * per_cat + g * 4096
+                ranges.append((lo, lo + 4096))
+        checked, equal, n_ref_hits, dt_cpu = 0, True, 0, 0.0
+        for lo, hi in ranges:
+            t0 = time.perf_counter()
+            ids, ff, rec, sk = ref.enumerate_mt(cats, gliders, lo, hi, gens, interval, hi - lo, 0)
+            dt_cpu += time.perf_counter() - t0
+            sub = hits[(hits["id"] >= lo) & (hits["id"] < hi)]
+            equal = equal and len(sub) == len(ids) and bool((sub["id"] == ids).all() and (sub["g_first_false"] == ff).all()
+                                                             and (sub["g_recovered"] == rec).all())
+            checked += hi - lo
+            n_ref_hits += len(ids)
+        out["cpu_baseline"] = {"placements_per_s": checked / dt_cpu, "cores": ref.threads(), "kind": "reference",
+                               "sample": f"{checked} placement ids = 1/16 of the space, 2 glider variants of every one of the 32 "
+                                         f"catalysts, {dt_cpu:.2f} s on {ref.threads()} threads"}
+        out["parity"] = {"checked": int(checked), "equal": bool(equal), "vs": "reference", "reference_hits": int(n_ref_hits),
+                         "what": "hit records (id, g_first_false, g_recovered) of the sampled id ranges against the reference enumeration"}
     return out
 
 
@@ -283,12 +302,18 @@ def next_rows(eng, p_int):
         out["weld_step"] = {"workload": f"LifeWeld::Step x {gens} generations on {n} records (2048 B each), in place", "ms": ms,
                             "value": n * 4096.0 * gens / (ms * 1e-3) / 1e9, "unit": "Gcell/s"}
         if ref is not None:
-            m = 1 << 11
+            m = 1 << 14
             t0 = time.perf_counter()
-            ref.weld_step(recs[:m], gens)
+            want = ref.weld_step_batch(recs[:m], gens, 0)
             dt = time.perf_counter() - t0
-            out["weld_step"]["cpu_baseline"] = {"value": m * 4096.0 * gens / dt / 1e9, "unit": "Gcell/s", "cores": 1,
-                                                "kind": "reference", "sample": f"{m} records x {gens} gens, {dt:.2f} s, 1 thread"}
+            got = np.empty((m, 4, 64), dtype=np.uint64)
+            eng.h2d(d, recs)  # the timing loop stepped the records in place: start again from the inputs
+            eng._check(eng.lib.lifeb200_weld_step_batch_dev(eng._h, d, n, gens))
+            eng.d2h(got, d)
+            eng.sync()
+            out["weld_step"]["cpu_baseline"] = {"value": m * 4096.0 * gens / dt / 1e9, "unit": "Gcell/s", "cores": ref.threads(),
+                                                "kind": "reference", "sample": f"{m} records x {gens} gens, {dt:.2f} s, {ref.threads()} threads",
+                                                "equal_on_sample": bool((got == want).all())}
     finally:
         eng.free(d)
     n = 1 << 20
@@ -299,18 +324,18 @@ def next_rows(eng, p_int):
         out["get_hash"] = {"workload": f"GetHash (XXH3-64 of the 512-byte state) over {n} resident soups", "ms": ms,
                            "states_per_s": n / (ms * 1e-3), "hbm_gbs": n * 520 / (ms * 1e-3) / 1e9}
         if ref is not None:
-            m = 1 << 14
+            m = 1 << 18
             host = np.empty((m, 64), dtype=np.uint64)
             eng.d2h(host, d_s)
             got = np.empty(m, dtype=np.uint64)
             eng.d2h(got, d_h)
             eng.sync()
             t0 = time.perf_counter()
-            want = [ref.hash(host[i]) for i in range(m)]
+            want = ref.hash_batch(host, 0)
             dt = time.perf_counter() - t0
-            out["get_hash"]["cpu_baseline"] = {"states_per_s": m / dt, "cores": 1, "kind": "reference",
-                                               "sample": f"{m} states, {dt:.2f} s, 1 thread, one ctypes call per state",
-                                               "equal_on_sample": bool((np.array(want, dtype=np.uint64) == got).all())}
+            out["get_hash"]["cpu_baseline"] = {"states_per_s": m / dt, "cores": ref.threads(), "kind": "reference",
+                                               "sample": f"{m} states, {dt:.3f} s, {ref.threads()} threads (native loop over GetHash)",
+                                               "equal_on_sample": bool((want == got).all())}
     finally:
         eng.free(d_s)
         eng.free(d_h)
@@ -322,15 +347,18 @@ def next_rows(eng, p_int):
         out["interaction_counts"] = {"workload": f"InteractionCountsAndNext over {n} resident soups (4 planes out)", "ms": ms,
                                      "states_per_s": n / (ms * 1e-3), "hbm_gbs": n * 2560 / (ms * 1e-3) / 1e9}
         if ref is not None:
-            m = 1 << 12
+            m = 1 << 16
             host = np.empty((m, 64), dtype=np.uint64)
             eng.d2h(host, d_s)
+            got = np.empty((m, 4, 64), dtype=np.uint64)
+            eng.d2h(got, d_p)
             eng.sync()
             t0 = time.perf_counter()
-            ref.interaction_counts(host)
+            want = ref.interaction_counts_batch(host, 0)
             dt = time.perf_counter() - t0
-            out["interaction_counts"]["cpu_baseline"] = {"states_per_s": m / dt, "cores": 1, "kind": "reference",
-                                                         "sample": f"{m} states, {dt:.2f} s, 1 thread"}
+            out["interaction_counts"]["cpu_baseline"] = {"states_per_s": m / dt, "cores": ref.threads(), "kind": "reference",
+                                                         "sample": f"{m} states, {dt:.3f} s, {ref.threads()} threads",
+                                                         "equal_on_sample": bool((want == got).all())}
     finally:
         eng.free(d_s)
         eng.free(d_p)
