@@ -167,15 +167,17 @@ struct Tile {
   uint32_t lo[W], hi[W];
 
   // sub = lane index inside the pattern's lane group (0..LPP-1)
-  __device__ __forceinline__ void load(const uint64_t* __restrict__ pat, int sub) {
+  // plain (coherent) vector loads, no __restrict__: several entry points step IN PLACE (in == out, records
+  // updated where they lie), and a non-coherent ld.global.nc of memory the same kernel later writes is undefined
+  __device__ __forceinline__ void load(const uint64_t* pat, int sub) {
     const uint4* p = reinterpret_cast<const uint4*>(pat + sub * W);
 #pragma unroll
     for (int k = 0; k < W / 2; k++) {
-      uint4 v = __ldg(p + k);
+      uint4 v = p[k];
       lo[2 * k] = v.x; hi[2 * k] = v.y; lo[2 * k + 1] = v.z; hi[2 * k + 1] = v.w;
     }
   }
-  __device__ __forceinline__ void store(uint64_t* __restrict__ pat, int sub) const {
+  __device__ __forceinline__ void store(uint64_t* pat, int sub) const {
     uint4* p = reinterpret_cast<uint4*>(pat + sub * W);
 #pragma unroll
     for (int k = 0; k < W / 2; k++) p[k] = make_uint4(lo[2 * k], hi[2 * k], lo[2 * k + 1], hi[2 * k + 1]);

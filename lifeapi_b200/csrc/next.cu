@@ -5,6 +5,7 @@
 #include <algorithm>
 
 #include "ctx.h"
+#include "host_pipeline.cuh"
 #include "life_core.cuh"
 #include "xxh3_keys.h"
 
@@ -190,12 +191,33 @@ static unsigned grid_hash(const lifeb200_ctx* ctx, size_t n) {
 
 extern "C" {
 
+static int launch_weld(lifeb200_ctx* ctx, cudaStream_t st, uint64_t* records, size_t n, unsigned gens) {
+  int lpp = std::max(8, effective_lpp(ctx));  // 8 tiles live: keep W <= 8
+  LIFEB200_DISPATCH_LPP_MIN4(lpp, (weld_step_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, st>>>(records, n, gens)));
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
 int lifeb200_weld_step_batch_dev(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens) {
   LIFEB200_CHECK_CTX(ctx);
   if (n == 0 || gens == 0) return LIFEB200_OK;
   if (!records || !aligned16(records)) return set_error(LIFEB200_E_ARG, "bad record pointer");
-  int lpp = std::max(8, effective_lpp(ctx));  // 8 tiles live: keep W <= 8
-  LIFEB200_DISPATCH_LPP_MIN4(lpp, (weld_step_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, ctx->stream>>>(records, n, gens)));
+  return launch_weld(ctx, ctx->stream, records, n, gens);
+}
+
+int lifeb200_weld_step_batch_host(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0 || gens == 0) return LIFEB200_OK;
+  if (!records) return set_error(LIFEB200_E_ARG, "null record pointer");
+  return host_pipeline_impl(ctx, records, records, n, 4 * LIFEB200_PATTERN_BYTES, 4 * LIFEB200_PATTERN_BYTES, false, (size_t)1 << 14,
+                            [&](cudaStream_t st, const uint64_t* din, uint64_t*, size_t cnt) -> int {
+                              return launch_weld(ctx, st, const_cast<uint64_t*>(din), cnt, gens);
+                            });
+}
+
+static int launch_interaction(lifeb200_ctx* ctx, cudaStream_t st, const uint64_t* in, uint64_t* planes, size_t n) {
+  int lpp = ctx->lpp ? std::max(8, ctx->lpp) : 32;
+  LIFEB200_DISPATCH_LPP_MIN4(lpp, (interaction_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, st>>>(in, planes, n)));
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
 }
@@ -204,10 +226,17 @@ int lifeb200_interaction_counts_dev(lifeb200_ctx* ctx, const uint64_t* in, uint6
   LIFEB200_CHECK_CTX(ctx);
   if (n == 0) return LIFEB200_OK;
   if (!in || !planes || !aligned16(in) || !aligned16(planes)) return set_error(LIFEB200_E_ARG, "null or misaligned pointer");
-  int lpp = ctx->lpp ? std::max(8, ctx->lpp) : 32;
-  LIFEB200_DISPATCH_LPP_MIN4(lpp, (interaction_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, ctx->stream>>>(in, planes, n)));
-  LIFEB200_LAUNCHED(ctx);
-  return LIFEB200_OK;
+  return launch_interaction(ctx, ctx->stream, in, planes, n);
+}
+
+int lifeb200_interaction_counts_host(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (!in || !planes) return set_error(LIFEB200_E_ARG, "null pointer");
+  return host_pipeline_impl(ctx, in, planes, n, LIFEB200_PATTERN_BYTES, 4 * LIFEB200_PATTERN_BYTES, true, (size_t)1 << 15,
+                            [&](cudaStream_t st, const uint64_t* din, uint64_t* dout, size_t cnt) -> int {
+                              return launch_interaction(ctx, st, din, dout, cnt);
+                            });
 }
 
 int lifeb200_hash_batch_dev(lifeb200_ctx* ctx, const uint64_t* patterns, uint64_t* hashes, size_t n) {

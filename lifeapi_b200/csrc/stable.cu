@@ -12,6 +12,7 @@
 #include <algorithm>
 
 #include "ctx.h"
+#include "host_pipeline.cuh"
 #include "generated/circuits.cuh"
 #include "life_core.cuh"
 
@@ -440,6 +441,18 @@ int lifeb200_stable_vulnerable_dev(lifeb200_ctx* ctx, const uint64_t* records, u
   return LIFEB200_OK;
 }
 
+int lifeb200_stable_vulnerable_host(lifeb200_ctx* ctx, const uint64_t* records, uint64_t* out, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (!records || !out) return set_error(LIFEB200_E_ARG, "null pointer");
+  return host_pipeline_impl(ctx, records, out, n, LIFEB200_STABLE_BYTES, LIFEB200_PATTERN_BYTES, true, (size_t)1 << 13,
+                            [&](cudaStream_t st, const uint64_t* din, uint64_t* dout, size_t cnt) -> int {
+                              stable_vulnerable_kernel<<<grid_s(cnt), kBlockS, 0, st>>>(din, cnt, dout);
+                              LIFEB200_LAUNCHED(ctx);
+                              return LIFEB200_OK;
+                            });
+}
+
 int lifeb200_unknown_step_refined_dev(lifeb200_ctx* ctx, const uint64_t* records, const uint64_t* current_on,
                                       const uint64_t* current_unknown, size_t n, int variant, uint64_t* next_on,
                                       uint64_t* next_unknown, uint64_t* next_unknown_stable) {
@@ -453,6 +466,49 @@ int lifeb200_unknown_step_refined_dev(lifeb200_ctx* ctx, const uint64_t* records
                                                                next_unknown, next_unknown_stable);
   LIFEB200_LAUNCHED(ctx);
   return LIFEB200_OK;
+}
+
+// Host form: the three inputs of a chunk are staged side by side in the slot's first buffer, the three output
+// planes in its second (records | current_on | current_unknown  ->  next_on | next_unknown | next_unknown_stable).
+int lifeb200_unknown_step_refined_host(lifeb200_ctx* ctx, const uint64_t* records, const uint64_t* current_on,
+                                       const uint64_t* current_unknown, size_t n, int variant, uint64_t* next_on,
+                                       uint64_t* next_unknown, uint64_t* next_unknown_stable) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (variant != 0 && variant != 1) return set_error(LIFEB200_E_ARG, "variant must be 0 (refined_m) or 1 (refined)");
+  if (n == 0) return LIFEB200_OK;
+  const void* ptrs[] = {records, current_on, current_unknown, next_on, next_unknown, next_unknown_stable};
+  for (const void* p : ptrs)
+    if (!p) return set_error(LIFEB200_E_ARG, "null pointer");
+  const size_t chunk = std::min<size_t>(n, (size_t)1 << 13);
+  const size_t nchunks = (n + chunk - 1) / chunk;
+  const int used = (int)std::min<size_t>(kSlots, nchunks);
+  for (int s = 0; s < used; s++)
+    if (int rc = ensure_slot(ctx, s, chunk * (LIFEB200_STABLE_BYTES + 2 * LIFEB200_PATTERN_BYTES), chunk * 3 * LIFEB200_PATTERN_BYTES)) return rc;
+  auto body = [&]() -> int {
+    for (size_t c = 0; c < nchunks; c++) {
+      Slot& sl = ctx->slots[c % kSlots];
+      const size_t off = c * chunk, cnt = std::min(chunk, n - off), pb = cnt * LIFEB200_PATTERN_BYTES;
+      uint64_t* d_rec = static_cast<uint64_t*>(sl.dbuf);
+      uint64_t* d_on = d_rec + chunk * LIFEB200_STABLE_WORDS;
+      uint64_t* d_unk = d_on + chunk * kN;
+      uint64_t* o_on = static_cast<uint64_t*>(sl.dbuf2);
+      uint64_t* o_unk = o_on + chunk * kN;
+      uint64_t* o_st = o_unk + chunk * kN;
+      LIFEB200_CUDA(cudaMemcpyAsync(d_rec, records + off * LIFEB200_STABLE_WORDS, cnt * LIFEB200_STABLE_BYTES, cudaMemcpyHostToDevice, sl.stream));
+      LIFEB200_CUDA(cudaMemcpyAsync(d_on, current_on + off * kN, pb, cudaMemcpyHostToDevice, sl.stream));
+      LIFEB200_CUDA(cudaMemcpyAsync(d_unk, current_unknown + off * kN, pb, cudaMemcpyHostToDevice, sl.stream));
+      refined_step_kernel<<<grid_s(cnt), kBlockS, 0, sl.stream>>>(d_rec, d_on, d_unk, cnt, variant, o_on, o_unk, o_st);
+      LIFEB200_LAUNCHED(ctx);
+      LIFEB200_CUDA(cudaMemcpyAsync(next_on + off * kN, o_on, pb, cudaMemcpyDeviceToHost, sl.stream));
+      LIFEB200_CUDA(cudaMemcpyAsync(next_unknown + off * kN, o_unk, pb, cudaMemcpyDeviceToHost, sl.stream));
+      LIFEB200_CUDA(cudaMemcpyAsync(next_unknown_stable + off * kN, o_st, pb, cudaMemcpyDeviceToHost, sl.stream));
+    }
+    for (int s = 0; s < used; s++) LIFEB200_CUDA(cudaStreamSynchronize(ctx->slots[s].stream));
+    return LIFEB200_OK;
+  };
+  const int rc = body();
+  if (rc) drain_slots(ctx, used);
+  return rc;
 }
 
 }  // extern "C"

@@ -6,6 +6,7 @@
 #include "ctx.h"
 #include "life_core.cuh"
 #include "life_multi.cuh"
+#include "host_pipeline.cuh"
 
 namespace lifeb200 {
 
@@ -28,7 +29,7 @@ constexpr unsigned kInterleaveFrom = 36, kMultiFrom = 20;
 // Each warp owns 32/LPP whole patterns; `gens` generations run in registers between one
 // 128-bit vectorised load and one 128-bit vectorised store per 16 bytes of state.
 template <int LPP>
-__global__ void __launch_bounds__(kStepBlock, 1) step_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
+__global__ void __launch_bounds__(kStepBlock, 1) step_kernel(const uint64_t* in, uint64_t* out,
                                                               size_t n, unsigned gens, bool interleaved) {
   const size_t gid = (size_t)blockIdx.x * kStepBlock + threadIdx.x;
   const size_t p = gid / LPP;
@@ -55,7 +56,7 @@ __global__ void __launch_bounds__(kStepBlock, 1) step_kernel(const uint64_t* __r
 
 // P = M/2 patterns per group of 8 lanes in the row-class layout of life_multi.cuh.
 template <int M>
-__global__ void __launch_bounds__(kStepBlock, 1) step_kernel_x(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
+__global__ void __launch_bounds__(kStepBlock, 1) step_kernel_x(const uint64_t* in, uint64_t* out,
                                                                 size_t n, unsigned gens) {
   constexpr int P = M / 2;
   const size_t gid = (size_t)blockIdx.x * kStepBlock + threadIdx.x;
@@ -68,7 +69,7 @@ __global__ void __launch_bounds__(kStepBlock, 1) step_kernel_x(const uint64_t* _
 #pragma unroll
     for (int s = 0; s < P; s++) {
       uint4 v = make_uint4(0, 0, 0, 0);  // groups past the end step empty patterns (they still shuffle)
-      if (p0 + s < n) v = __ldg(reinterpret_cast<const uint4*>(in + (p0 + s) * kN + sub * 8 + c));
+      if (p0 + s < n) v = *reinterpret_cast<const uint4*>(in + (p0 + s) * kN + sub * 8 + c);  // coherent: in may be out
       wa[s] = ((uint64_t)v.y << 32) | v.x;
       wb[s] = ((uint64_t)v.w << 32) | v.z;
     }
@@ -187,60 +188,6 @@ int launch_ncount(lifeb200_ctx* ctx, cudaStream_t st, const uint64_t* in, uint64
   return LIFEB200_OK;
 }
 
-// Host-pointer pipeline: chunk c uses slot c % kSlots; each slot's stream runs H2D -> kernel -> D2H,
-// so copies of neighbouring chunks overlap the kernel of the current one.  What stays exposed is the
-// first chunk's upload and the last chunk's download, so a large batch starts and ends with small
-// chunks (4 Ki, then 20 Ki patterns: each still uploads in less time than its predecessor computes)
-// and runs 64 Ki-pattern chunks (32 MiB of state) in between.
-static std::vector<size_t> chunk_plan(size_t n) {
-  constexpr size_t kBig = (size_t)1 << 16, kEdge0 = (size_t)1 << 12, kEdge1 = (size_t)20 << 10;
-  std::vector<size_t> plan;
-  if (n <= kEdge0) {
-    plan.push_back(n);
-  } else if (n < 4 * kBig) {
-    for (size_t off = 0; off < n; off += kBig) plan.push_back(std::min(kBig, n - off));
-  } else {
-    plan.push_back(kEdge0);
-    plan.push_back(kEdge1);
-    for (size_t left = n - 2 * (kEdge0 + kEdge1); left > 0;) {
-      const size_t c = std::min(kBig, left);
-      plan.push_back(c);
-      left -= c;
-    }
-    plan.push_back(kEdge1);
-    plan.push_back(kEdge0);
-  }
-  return plan;
-}
-
-template <class LaunchFn>
-int host_pipeline(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n, size_t in_bytes_per, size_t out_bytes_per,
-                  bool out_separate, LaunchFn launch) {
-  if (n == 0) return LIFEB200_OK;
-  const std::vector<size_t> plan = chunk_plan(n);
-  const size_t chunk = *std::max_element(plan.begin(), plan.end());
-  int used = (int)std::min<size_t>(kSlots, plan.size());
-  for (int s = 0; s < used; s++) {
-    int rc = ensure_slot(ctx, s, chunk * in_bytes_per, out_separate ? chunk * out_bytes_per : 0);
-    if (rc) return rc;
-  }
-  size_t off = 0;
-  for (size_t c = 0; c < plan.size(); c++) {
-    Slot& sl = ctx->slots[c % kSlots];
-    const size_t cnt = plan[c];
-    const char* src = reinterpret_cast<const char*>(in) + off * in_bytes_per;
-    char* dst = reinterpret_cast<char*>(out) + off * out_bytes_per;
-    LIFEB200_CUDA(cudaMemcpyAsync(sl.dbuf, src, cnt * in_bytes_per, cudaMemcpyHostToDevice, sl.stream));
-    void* dout = out_separate ? sl.dbuf2 : sl.dbuf;
-    int rc = launch(sl.stream, reinterpret_cast<const uint64_t*>(sl.dbuf), reinterpret_cast<uint64_t*>(dout), cnt);
-    if (rc) return rc;
-    LIFEB200_CUDA(cudaMemcpyAsync(dst, dout, cnt * out_bytes_per, cudaMemcpyDeviceToHost, sl.stream));
-    off += cnt;
-  }
-  for (int s = 0; s < used; s++) LIFEB200_CUDA(cudaStreamSynchronize(ctx->slots[s].stream));
-  return LIFEB200_OK;
-}
-
 }  // namespace lifeb200
 
 using namespace lifeb200;
@@ -252,6 +199,8 @@ int lifeb200_step_batch_dev(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* out
   if (n == 0) return LIFEB200_OK;
   if (!in || !out) return set_error(LIFEB200_E_ARG, "null pattern pointer");
   if (!aligned16(in) || !aligned16(out)) return set_error(LIFEB200_E_ARG, "pattern pointers must be 16-byte aligned");
+  if (in != out && in < out + n * kN && out < in + n * kN)
+    return set_error(LIFEB200_E_ARG, "in and out overlap partially (in == out is the only aliasing allowed)");
   if (gens == 0) {
     if (in != out)
       LIFEB200_CUDA(cudaMemcpyAsync(out, in, n * LIFEB200_PATTERN_BYTES, cudaMemcpyDeviceToDevice, ctx->stream));

@@ -9,6 +9,7 @@
 #include <algorithm>
 
 #include "ctx.h"
+#include "host_pipeline.cuh"
 #include "generated/circuits.cuh"
 #include "life_core.cuh"
 #include "life_three.cuh"
@@ -44,10 +45,10 @@ __device__ __forceinline__ void unknown_step_tile(Tile<LPP>& s, Tile<LPP>& u, in
 // exposed (config 3, 16 generations: 0.816 ms = 16 x 0.047 ms of stepping + 0.067 ms of load / store): every
 // CTA of a wave takes the same time, so co-resident CTAs load, step and store in lockstep and nothing overlaps.
 template <int LPP, bool IL>
-__global__ void __launch_bounds__(kBlockU, 1) unknown_step_kernel(const uint64_t* __restrict__ state_in,
-                                                               const uint64_t* __restrict__ unknown_in,
-                                                               uint64_t* __restrict__ state_out,
-                                                               uint64_t* __restrict__ unknown_out, size_t n,
+__global__ void __launch_bounds__(kBlockU, 1) unknown_step_kernel(const uint64_t* state_in,
+                                                               const uint64_t* unknown_in,
+                                                               uint64_t* state_out,
+                                                               uint64_t* unknown_out, size_t n,
                                                                unsigned gens, int force_literal) {
   constexpr bool kPrefetch = LPP >= 16;  // 2 x W more registers; 8 or 4 lanes per pattern have none to spare
   const size_t gid = (size_t)blockIdx.x * kBlockU + threadIdx.x;
@@ -217,14 +218,28 @@ int lifeb200_unknown_step_batch_host(lifeb200_ctx* ctx, const uint64_t* state_in
   return LIFEB200_OK;
 }
 
+static int launch_history(lifeb200_ctx* ctx, cudaStream_t st, uint64_t* records, size_t n, unsigned gens) {
+  int lpp = std::max(4, effective_lpp(ctx));
+  LIFEB200_DISPATCH_LPP_MIN4(lpp, (history_step_kernel<LPP><<<grid_u(n, LPP), kBlockU, 0, st>>>(records, n, gens)));
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
 int lifeb200_history_step_batch_dev(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens) {
   LIFEB200_CHECK_CTX(ctx);
   if (n == 0 || gens == 0) return LIFEB200_OK;
   if (!records || !aligned16(records)) return set_error(LIFEB200_E_ARG, "bad record pointer");
-  int lpp = std::max(4, effective_lpp(ctx));
-  LIFEB200_DISPATCH_LPP_MIN4(lpp, (history_step_kernel<LPP><<<grid_u(n, LPP), kBlockU, 0, ctx->stream>>>(records, n, gens)));
-  LIFEB200_LAUNCHED(ctx);
-  return LIFEB200_OK;
+  return launch_history(ctx, ctx->stream, records, n, gens);
+}
+
+int lifeb200_history_step_batch_host(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0 || gens == 0) return LIFEB200_OK;
+  if (!records) return set_error(LIFEB200_E_ARG, "null record pointer");
+  return host_pipeline_impl(ctx, records, records, n, 4 * LIFEB200_PATTERN_BYTES, 4 * LIFEB200_PATTERN_BYTES, false, (size_t)1 << 14,
+                            [&](cudaStream_t st, const uint64_t* din, uint64_t*, size_t cnt) -> int {
+                              return launch_history(ctx, st, const_cast<uint64_t*>(din), cnt, gens);
+                            });
 }
 
 }  // extern "C"
