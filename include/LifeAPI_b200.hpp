@@ -22,10 +22,13 @@
 #pragma once
 
 #include <bit>
+#include <cmath>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ostream>
+#include <random>
 #include <string>
 #include <utility>
 #include <vector>
@@ -33,6 +36,24 @@
 #include "lifeapi_b200.h"
 
 constexpr int N = 64;  // LifeAPI.hpp:12
+
+constexpr unsigned torus_wrap(int x) { return x & (N - 1); }  // LifeAPI.hpp:14-16 (valid for negative x)
+
+// LifeAPI.hpp:18-23: the soup source of RandomState -- 64 draws uniform in [2^61, 2^62] from a mt19937_64 seeded by
+// random_device.  PRNG::Seed(s) makes a run reproducible (the reference has no such knob; tests use it).
+namespace PRNG {
+inline std::mt19937_64& Engine() {
+  static std::mt19937_64 e2{std::random_device{}()};
+  return e2;
+}
+inline void Seed(uint64_t s) { Engine().seed(s); }
+inline uint64_t Draw() {
+  static std::uniform_int_distribution<uint64_t> dist(std::llround(std::pow(2, 61)), std::llround(std::pow(2, 62)));
+  return dist(Engine());
+}
+}  // namespace PRNG
+
+enum class InitializedTag { UNINITIALIZED };  // LifeAPI.hpp:37
 
 namespace lifeb200 {
 
@@ -63,14 +84,32 @@ struct alignas(64) LifeState {
   uint64_t state[N];
 
   constexpr LifeState() : state{0} {}
+  explicit constexpr LifeState(InitializedTag) {}  // LifeAPI.hpp:47: planes every word of which is about to be written
+  LifeState& operator=(bool) = delete;             // :55 avoid accidentally coercing from a bool
+  LifeState(const LifeState&) = default;
+  LifeState& operator=(const LifeState&) = default;
 
   uint64_t& operator[](unsigned i) { return state[i]; }
   uint64_t operator[](unsigned i) const { return state[i]; }
 
+  static constexpr LifeState Cell(std::pair<int, int> cell) {  // LifeAPI.hpp:57-61
+    LifeState result;
+    result.Set(cell.first, cell.second);
+    return result;
+  }
+  static LifeState RandomState() {  // LifeAPI.hpp:63-69
+    LifeState result;
+    for (unsigned i = 0; i < (unsigned)N; i++) result[i] = PRNG::Draw();
+    return result;
+  }
+
   // ---- cell access (LifeAPI.hpp:131-146): word = column x, bit = row y ----------------------
-  void Set(unsigned x, unsigned y) { state[x & 63] |= 1ULL << (y & 63); }
-  void Erase(unsigned x, unsigned y) { state[x & 63] &= ~(1ULL << (y & 63)); }
-  bool Get(unsigned x, unsigned y) const { return (state[x & 63] >> (y & 63)) & 1ULL; }
+  constexpr void Set(unsigned x, unsigned y) { state[x & 63] |= 1ULL << (y & 63); }
+  constexpr void Erase(unsigned x, unsigned y) { state[x & 63] &= ~(1ULL << (y & 63)); }
+  constexpr bool Get(unsigned x, unsigned y) const { return (state[x & 63] >> (y & 63)) & 1ULL; }
+  void Set(std::pair<int, int> c) { Set((unsigned)c.first, (unsigned)c.second); }
+  void Erase(std::pair<int, int> c) { Erase((unsigned)c.first, (unsigned)c.second); }
+  bool Get(std::pair<int, int> c) const { return Get((unsigned)c.first, (unsigned)c.second); }
 
   // ---- plane algebra (LifeAPI.hpp:213-298) --------------------------------------------------
   bool operator==(const LifeState& o) const { return std::memcmp(state, o.state, sizeof state) == 0; }
@@ -93,6 +132,8 @@ struct alignas(64) LifeState {
     return r;
   }
   void Move(int x, int y) { *this = Moved(x, y); }
+  void Move(std::pair<int, int> vec) { Move(vec.first, vec.second); }                            // LifeAPI.hpp:697
+  LifeState Moved(std::pair<int, int> vec) const { return Moved(vec.first, vec.second); }        // :719-721
   LifeState ZOI() const {
     uint64_t col[N];
     for (int i = 0; i < N; i++) col[i] = state[i] | std::rotl(state[i], 1) | std::rotr(state[i], 1);
@@ -102,20 +143,29 @@ struct alignas(64) LifeState {
   }
   LifeState GetBoundary() const { return ZOI() & ~*this; }
 
-  // ---- RLE input (Parsing.hpp:143-198 semantics: a bare '$' counts as one row) ---------------
-  static LifeState Parse(const std::string& rle, int dx = 0, int dy = 0) {
+  // ---- RLE input: LifeState::Parse (Parsing.hpp:141-198) through the library's parser, which follows the
+  // reference's GenericParse character for character (header lines dropped, counts carried over spaces and
+  // newlines, only 'o' sets a cell, unknown characters advance x, the 129-row abort); then Move(dx, dy)
+  static LifeState Parse(const std::string& rle) {
     LifeState r;
-    int x = 0, y = 0, cnt = 0;
-    for (char ch : rle) {
-      if (ch >= '0' && ch <= '9') { cnt = cnt * 10 + (ch - '0'); continue; }
-      const int k = cnt ? cnt : 1;
-      cnt = 0;
-      if (ch == 'o' || ch == 'A') { for (int j = 0; j < k; j++) r.Set((unsigned)(x + j + dx), (unsigned)(y + dy)); x += k; }
-      else if (ch == 'b' || ch == '.') x += k;
-      else if (ch == '$') { y += k; x = 0; }
-      else if (ch == '!') break;
-    }
+    lifeb200::Check(lifeb200_parse_rle(rle.c_str(), r.state), "LifeState::Parse");
     return r;
+  }
+  static LifeState Parse(const std::string& rle, int dx, int dy) { return Parse(rle).Moved(dx, dy); }
+
+  // ---- per-cell queries (LifeAPI.hpp:889-895,1042-1064) --------------------------------------
+  unsigned CountNeighboursWithCenter(std::pair<int, int> cell) const {
+    unsigned result = 0;
+    for (unsigned i = 0; i <= 2; i++) {
+      const uint64_t column = std::rotr(state[torus_wrap(cell.first + (int)i - 1)], cell.second - 1);
+      result += (unsigned)std::popcount(column & 0b111);
+    }
+    return result;
+  }
+  unsigned CountNeighbours(std::pair<int, int> cell) const { return CountNeighboursWithCenter(cell) - (Get(cell) ? 1 : 0); }
+  bool StepFor(std::pair<int, int> cell) const {
+    const unsigned count = CountNeighbours(cell);
+    return Get(cell) ? (count == 2 || count == 3) : count == 3;
   }
 
   // ---- adder conventions (LifeAPI.hpp:822-833,850-864): (sum, carry) first, by reference ------
@@ -137,7 +187,15 @@ struct alignas(64) LifeState {
   void Step(unsigned numIters) {
     lifeb200::Check(lifeb200_step_batch_host(lifeb200::DefaultContext(), state, state, 1, numIters), "LifeState::Step");
   }
-  void StepAlt() { Step(1u); }  // same function, second formulation in the reference (:1218-1254)
+  // StepAlt (LifeAPI.hpp:1218-1254): the reference's SECOND formulation of the same function -- two full adders
+  // over the column counts, cc ^= fc & cs, (fs ^ cc) & (fc ^ cs ^ cc) & (a | fs).  Here too it is a second circuit:
+  // the `next` plane of the interaction kernel, which evaluates exactly that form (csrc/next.cu), whereas Step()
+  // runs the pair-shared select of the step kernels.  tests/StepAltTest.cpp compares the two, as in the reference.
+  void StepAlt() {
+    alignas(64) uint64_t planes[4 * N];
+    lifeb200::Check(lifeb200_interaction_counts_host(lifeb200::DefaultContext(), state, planes, 1), "LifeState::StepAlt");
+    std::memcpy(state, planes + 3 * N, sizeof state);
+  }
   [[nodiscard]] LifeState Stepped() const { LifeState r = *this; r.Step(); return r; }
   [[nodiscard]] LifeState Stepped(unsigned numIters) const { LifeState r = *this; r.Step(numIters); return r; }
 
@@ -158,17 +216,8 @@ struct alignas(64) LifeState {
 
   // InteractionCounts / InteractionCountsAndNext (LifeAPI.hpp:956-1040)
   void InteractionCountsAndNext(LifeState& out1, LifeState& out2, LifeState& outMore, LifeState& next) const {
-    lifeb200_ctx* ctx = lifeb200::DefaultContext();
-    void *d = nullptr, *o = nullptr;
     alignas(64) uint64_t planes[4 * N];
-    lifeb200::Check(lifeb200_malloc(ctx, &d, sizeof state), "malloc");
-    lifeb200::Check(lifeb200_malloc(ctx, &o, sizeof planes), "malloc");
-    lifeb200::Check(lifeb200_memcpy_h2d(ctx, d, state, sizeof state), "h2d");
-    lifeb200::Check(lifeb200_interaction_counts_dev(ctx, static_cast<const uint64_t*>(d), static_cast<uint64_t*>(o), 1), "InteractionCounts");
-    lifeb200::Check(lifeb200_memcpy_d2h(ctx, planes, o, sizeof planes), "d2h");
-    lifeb200::Check(lifeb200_sync(ctx), "sync");
-    lifeb200_free(ctx, d);
-    lifeb200_free(ctx, o);
+    lifeb200::Check(lifeb200_interaction_counts_host(lifeb200::DefaultContext(), state, planes, 1), "InteractionCounts");
     std::memcpy(out1.state, planes, 512); std::memcpy(out2.state, planes + N, 512);
     std::memcpy(outMore.state, planes + 2 * N, 512); std::memcpy(next.state, planes + 3 * N, 512);
   }
@@ -229,8 +278,23 @@ struct alignas(64) LifeState {
   }
 
   bool Contains(const LifeTarget& target) const;  // LifeTarget.hpp:44-51 (defined below)
+  bool Contains(const LifeTarget& target, int dx, int dy) const;  // LifeTarget.hpp:38-42 (defined below)
   bool Contains(const LifeState& pat) const { return (*this & pat) == pat; }                 // :388-397
   bool AreDisjoint(const LifeState& pat) const { return (*this & pat).IsEmpty(); }          // :377-386
+  bool Contains(const LifeState& pat, int targetDx, int targetDy) const {                    // :399-409
+    const int dy = (int)torus_wrap(targetDy);
+    for (unsigned i = 0; i < (unsigned)N; i++)
+      if ((std::rotr(state[torus_wrap((int)i + targetDx)], dy) & pat[i]) != pat[i]) return false;
+    return true;
+  }
+  bool AreDisjoint(const LifeState& pat, int targetDx, int targetDy) const {                 // :411-422
+    const int dy = (int)torus_wrap(targetDy);
+    for (unsigned i = 0; i < (unsigned)N; i++)
+      if (((~std::rotr(state[torus_wrap((int)i + targetDx)], dy)) & pat[i]) != pat[i]) return false;
+    return true;
+  }
+
+  friend std::ostream& operator<<(std::ostream& os, LifeState const& self) { return os << self.RLE(); }  // :1176-1178
 };
 static_assert(sizeof(LifeState) == 512 && alignof(LifeState) == 64, "LifeState layout (LifeAPI.hpp:39-40)");
 
@@ -248,6 +312,10 @@ inline LifeState LifeState::Match(const LifeTarget& t) const {
   LifeState r;
   lifeb200::Check(lifeb200_match_target_batch_host(lifeb200::DefaultContext(), state, 1, t.wanted.state, 1, r.state), "Match(LifeTarget)");
   return r;
+}
+
+inline bool LifeState::Contains(const LifeTarget& t, int dx, int dy) const {
+  return Contains(t.wanted, dx, dy) && AreDisjoint(t.unwanted, dx, dy);
 }
 
 inline bool LifeState::Contains(const LifeTarget& t) const {
@@ -310,14 +378,7 @@ struct LifeHistory {
   }
   // build-defined accumulate step: n times { state.Step(); history |= state; } in one launch
   void StepAccumulate(unsigned n = 1) {
-    lifeb200_ctx* ctx = lifeb200::DefaultContext();
-    void* d = nullptr;
-    lifeb200::Check(lifeb200_malloc(ctx, &d, sizeof *this), "malloc");
-    lifeb200::Check(lifeb200_memcpy_h2d(ctx, d, this, sizeof *this), "h2d");
-    lifeb200::Check(lifeb200_history_step_batch_dev(ctx, static_cast<uint64_t*>(d), 1, n), "StepAccumulate");
-    lifeb200::Check(lifeb200_memcpy_d2h(ctx, this, d, sizeof *this), "d2h");
-    lifeb200::Check(lifeb200_sync(ctx), "sync");
-    lifeb200::Check(lifeb200_free(ctx, d), "free");
+    lifeb200::Check(lifeb200_history_step_batch_host(lifeb200::DefaultContext(), state.state, 1, n), "StepAccumulate");
   }
 };
 static_assert(sizeof(LifeHistory) == 2048, "LifeHistory layout (LifeHistory.hpp:8-12)");
@@ -337,14 +398,7 @@ struct LifeWeld {
     return 3 * frozen2.GetHash() + (3 * frozen1.GetHash() + (3 * frozen0.GetHash() + state.GetHash()));
   }
   void Step(unsigned numIters = 1) {  // LifeWeld.hpp:169-186
-    lifeb200_ctx* ctx = lifeb200::DefaultContext();
-    void* d = nullptr;
-    lifeb200::Check(lifeb200_malloc(ctx, &d, sizeof *this), "malloc");
-    lifeb200::Check(lifeb200_memcpy_h2d(ctx, d, this, sizeof *this), "h2d");
-    lifeb200::Check(lifeb200_weld_step_batch_dev(ctx, static_cast<uint64_t*>(d), 1, numIters), "LifeWeld::Step");
-    lifeb200::Check(lifeb200_memcpy_d2h(ctx, this, d, sizeof *this), "d2h");
-    lifeb200::Check(lifeb200_sync(ctx), "sync");
-    lifeb200::Check(lifeb200_free(ctx, d), "free");
+    lifeb200::Check(lifeb200_weld_step_batch_host(lifeb200::DefaultContext(), state.state, 1, numIters), "LifeWeld::Step");
   }
   LifeTarget ToTarget() const;  // LifeWeld.hpp:188-191 (defined after LifeTarget)
 };
@@ -386,17 +440,8 @@ struct LifeStable {
   PropagateResult Propagate() { return Run(LIFEB200_STABLE_PROPAGATE); }                        // :718-729
 
   LifeState Vulnerable() const {  // :366-412
-    lifeb200_ctx* ctx = lifeb200::DefaultContext();
-    void *d = nullptr, *o = nullptr;
     LifeState out;
-    lifeb200::Check(lifeb200_malloc(ctx, &d, sizeof *this), "malloc");
-    lifeb200::Check(lifeb200_malloc(ctx, &o, sizeof out), "malloc");
-    lifeb200::Check(lifeb200_memcpy_h2d(ctx, d, this, sizeof *this), "h2d");
-    lifeb200::Check(lifeb200_stable_vulnerable_dev(ctx, static_cast<const uint64_t*>(d), static_cast<uint64_t*>(o), 1), "Vulnerable");
-    lifeb200::Check(lifeb200_memcpy_d2h(ctx, out.state, o, sizeof out), "d2h");
-    lifeb200::Check(lifeb200_sync(ctx), "sync");
-    lifeb200_free(ctx, d);
-    lifeb200_free(ctx, o);
+    lifeb200::Check(lifeb200_stable_vulnerable_host(lifeb200::DefaultContext(), state.state, out.state, 1), "Vulnerable");
     return out;
   }
 

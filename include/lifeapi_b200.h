@@ -13,8 +13,12 @@
  *               (SURVEY.md 8b), so header wrappers abort on non-zero.
  *   *_dev     = pointers are DEVICE pointers on the context's GPU; work is enqueued on the
  *               context's stream and is asynchronous; call lifeb200_sync().
- *   *_host    = pointers are HOST pointers; the call stages through pinned buffers, overlaps
- *               copy and compute, and returns when the result is in the caller's buffer.
+ *   *_host    = pointers are HOST pointers; the batch is cut into chunks that go H2D -> kernel -> D2H on
+ *               three streams, straight from / to the caller's buffers, and the call returns when the
+ *               result is in the caller's buffer.  With PINNED buffers (lifeb200_host_alloc or
+ *               cudaHostRegister) the copies overlap the kernels; pageable buffers are correct but the
+ *               copies are staged by the driver and mostly serial.  On failure every copy has finished
+ *               (or been abandoned) before the call returns.
  *   There is no CPU fallback: without a usable CUDA device every compute call fails.
  */
 #ifndef LIFEAPI_B200_H
@@ -112,6 +116,21 @@ int lifeb200_step_match_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const u
                             unsigned stable_interval, lifeb200_hit* hits, size_t cap,
                             unsigned long long* n_hits);
 
+/* Host form: patterns (n x 512 B), targets (n_targets x 1024 B), target_index (n, may be NULL) and hits are HOST
+ * arrays; *n_hits (host) receives the count; LIFEB200_E_OVERFLOW if cap is too small (the first cap records, in id
+ * order, are still delivered). */
+int lifeb200_step_match_host(lifeb200_ctx* ctx, const uint64_t* patterns, const uint64_t* targets,
+                             const uint32_t* target_index, size_t n, size_t n_targets, uint64_t first_id, unsigned gens,
+                             unsigned stable_interval, lifeb200_hit* hits, size_t cap, uint64_t* n_hits);
+
+/* ---- A11  LifeState::Contains(const LifeTarget&, int dx, int dy) (LifeTarget.hpp:38-42 -> LifeAPI.hpp:399-422):
+ * contains[p] = 1 iff targets[p] (or the one shared target, n_targets == 1) placed at offset (dx, dy) fits
+ * states[p]: every wanted cell ON and every unwanted cell OFF in state word (i + dx) & 63 rotated right by dy. */
+int lifeb200_contains_target_batch_dev(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* targets,
+                                       size_t n_targets, int dx, int dy, uint8_t* contains);
+int lifeb200_contains_target_batch_host(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* targets,
+                                        size_t n_targets, int dx, int dy, uint8_t* contains);
+
 /* ---- A13 + A11  collision enumeration --------------------------
  * Placement id = ((c * n_projectiles + g) * 64 + dx) * 64 + dy.  pattern = catalyst[c] |
  * projectile[g].Moved(dx,dy) (LifeAPI.hpp:699-717, :247-253).  Placements whose ZOIs
@@ -170,6 +189,7 @@ int lifeb200_unknown_step_batch_host(lifeb200_ctx* ctx, const uint64_t* state_in
  * The reference has no stepping member; the build-defined step is, `gens` times,
  * state.Step() (LifeAPI.hpp:1196-1216) then history |= state (:255-260).  In place. */
 int lifeb200_history_step_batch_dev(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens);
+int lifeb200_history_step_batch_host(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens);
 
 /* ---- A10  LifeStable full-grid passes (LifeStable.hpp:366-729) ---------------------------
  * record = the 10 member planes in declaration order state, unknown, live2, live3, dead0, dead1,
@@ -195,6 +215,7 @@ int lifeb200_stable_pass_dev(lifeb200_ctx* ctx, uint64_t* records, size_t n, int
 int lifeb200_stable_pass_host(lifeb200_ctx* ctx, uint64_t* records, size_t n, int pass, uint8_t* flags);
 /* LifeStable::Vulnerable() (LifeStable.hpp:366-412 + stable_vulnerable.hpp): out = n x 512 B. */
 int lifeb200_stable_vulnerable_dev(lifeb200_ctx* ctx, const uint64_t* records, uint64_t* out, size_t n);
+int lifeb200_stable_vulnerable_host(lifeb200_ctx* ctx, const uint64_t* records, uint64_t* out, size_t n);
 
 /* ---- A9b  refined three-valued step (bitslicing/unknown_step_refined_m.hpp, variant 0; the
  * older unknown_step_refined.hpp cover, variant 1).  No consumer in the reference; inputs follow
@@ -205,15 +226,20 @@ int lifeb200_stable_vulnerable_dev(lifeb200_ctx* ctx, const uint64_t* records, u
 int lifeb200_unknown_step_refined_dev(lifeb200_ctx* ctx, const uint64_t* records, const uint64_t* current_on,
                                       const uint64_t* current_unknown, size_t n, int variant, uint64_t* next_on,
                                       uint64_t* next_unknown, uint64_t* next_unknown_stable);
+int lifeb200_unknown_step_refined_host(lifeb200_ctx* ctx, const uint64_t* records, const uint64_t* current_on,
+                                       const uint64_t* current_unknown, size_t n, int variant, uint64_t* next_on,
+                                       uint64_t* next_unknown, uint64_t* next_unknown_stable);
 
 /* ---- 8f "next" rows: the callers and formats either side of the stepping path ------------
  * LifeWeld::Step (LifeWeld.hpp:169-186): record = state, frozen2, frozen1, frozen0 = 2048 B
  * (LifeWeld.hpp:18-22); per generation the 3x3 count (bit3 dropped, as the reference does) plus
  * the frozen count feeds the B3/S23 rule.  In place, `gens` generations per launch. */
 int lifeb200_weld_step_batch_dev(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens);
+int lifeb200_weld_step_batch_host(lifeb200_ctx* ctx, uint64_t* records, size_t n, unsigned gens);
 /* LifeState::InteractionCountsAndNext (LifeAPI.hpp:997-1040; the first three planes are
  * InteractionCounts, :956-995): planes[p] = out1, out2, outMore, next (4 x 512 B). */
 int lifeb200_interaction_counts_dev(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n);
+int lifeb200_interaction_counts_host(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n);
 /* LifeState::GetHash (LifeAPI.hpp:373) = XXH3_64bits(state, 512) with the default secret
  * (xxHash v0.8.3, the reference's vendored submodule): hashes[p] for p < n. */
 int lifeb200_hash_batch_dev(lifeb200_ctx* ctx, const uint64_t* patterns, uint64_t* hashes, size_t n);

@@ -76,6 +76,15 @@ SIGNATURES = {
     "lifeb200_neighbour_count_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "lifeb200_step_match_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_uint64, C.c_uint, C.c_uint, _vp,
                                           C.c_size_t, _vp]),
+    "lifeb200_step_match_host": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_size_t, C.c_uint64, C.c_uint, C.c_uint, _vp,
+                                           C.c_size_t, _u64p]),
+    "lifeb200_contains_target_batch_dev": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, C.c_int, C.c_int, _vp]),
+    "lifeb200_contains_target_batch_host": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, C.c_int, C.c_int, _vp]),
+    "lifeb200_history_step_batch_host": (C.c_int, [_vp, _vp, C.c_size_t, C.c_uint]),
+    "lifeb200_stable_vulnerable_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_unknown_step_refined_host": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp, _vp]),
+    "lifeb200_weld_step_batch_host": (C.c_int, [_vp, _vp, C.c_size_t, C.c_uint]),
+    "lifeb200_interaction_counts_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "lifeb200_enumerate_collisions": (C.c_int, [_vp, _vp, C.c_uint, _vp, C.c_uint, C.c_uint64, C.c_uint64, C.c_uint,
                                                 C.c_uint, _vp, C.c_size_t, _u64p, _u64p]),
     "lifeb200_soup_survey": (C.c_int, [_vp, C.c_uint64, C.c_size_t, C.c_uint64, C.c_int, C.c_uint, _vp, C.c_size_t,

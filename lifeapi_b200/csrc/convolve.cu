@@ -13,6 +13,7 @@
 #include <algorithm>
 
 #include "ctx.h"
+#include "host_pipeline.cuh"
 #include "life_core.cuh"
 
 namespace lifeb200 {
@@ -212,6 +213,7 @@ int planes_host(lifeb200_ctx* ctx, const HostIn* ins, int n_ins, uint64_t* out, 
     int rc = ensure_slot(ctx, s, in_bytes, chunk * LIFEB200_PATTERN_BYTES);
     if (rc) return rc;
   }
+  auto body = [&]() -> int {
   for (size_t c = 0; c < nchunks; c++) {
     Slot& sl = ctx->slots[c % kSlots];
     const size_t off = c * chunk, cnt = std::min(chunk, n - off);
@@ -233,6 +235,37 @@ int planes_host(lifeb200_ctx* ctx, const HostIn* ins, int n_ins, uint64_t* out, 
   }
   for (int s = 0; s < used; s++) LIFEB200_CUDA(cudaStreamSynchronize(ctx->slots[s].stream));
   return LIFEB200_OK;
+  };
+  const int rc = body();
+  if (rc) drain_slots(ctx, used);  // nothing may still be copying towards the caller's buffers after the call returns
+  return rc;
+}
+
+// LifeState::Contains(const LifeTarget&, int dx, int dy) (LifeTarget.hpp:38-42 -> Contains(pat, dx, dy) and
+// AreDisjoint(pat, dx, dy), LifeAPI.hpp:399-422): the target sits at offset (dx, dy) of the state -- for every target
+// word i the state word (i + dx) & 63 rotated right by dy must hold every wanted cell and no unwanted one.  A warp
+// per state: lane L tests target words 2L, 2L + 1 (one coalesced 512-byte request per plane; the state words arrive
+// by the shifted index straight from global memory), one ballot folds the verdict.  HBM-bound: 512 B in, 1 B out.
+__global__ void __launch_bounds__(kBlockC) contains_shifted_kernel(const uint64_t* __restrict__ states, size_t n,
+                                                                   const uint64_t* __restrict__ targets, size_t n_targets,
+                                                                   int dx, int dy, uint8_t* __restrict__ out) {
+  const size_t p = ((size_t)blockIdx.x * kBlockC + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (p >= n) return;
+  const uint64_t* st = states + p * kN;
+  const uint64_t* tg = targets + (n_targets == 1 ? 0 : p) * 2 * kN;
+  const unsigned sy = (unsigned)dy & 63u;
+  uint64_t bad = 0;
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    const int i = 2 * lane + k;
+    const uint64_t w = tg[i], u = tg[kN + i];
+    const uint64_t v = st[(i + dx) & 63];
+    const uint64_t r = sy ? (v >> sy) | (v << (64u - sy)) : v;
+    bad |= (w & ~r) | (u & r);
+  }
+  const unsigned any = __ballot_sync(0xffffffffu, bad != 0);
+  if (lane == 0) out[p] = any ? 0 : 1;
 }
 
 static int check_pair(const void* a, size_t n_a, const void* b, size_t n_b, const void* out, size_t n, bool need_align) {
@@ -334,6 +367,63 @@ int lifeb200_interaction_offsets_host(lifeb200_ctx* ctx, const uint64_t* a, size
   return planes_host(ctx, ins, 2, out, n, [&](const uint64_t* const* d, uint64_t* dout, size_t cnt, cudaStream_t st) {
     interaction_offsets_kernel<<<grid_warps(cnt), kBlockC, 0, st>>>(d[0], n_a == 1 ? 1 : cnt, d[1], n_b == 1 ? 1 : cnt, dout, cnt);
   });
+}
+
+int lifeb200_contains_target_batch_dev(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* targets,
+                                       size_t n_targets, int dx, int dy, uint8_t* contains) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (!states || !targets || !contains) return set_error(LIFEB200_E_ARG, "null pointer");
+  if (n_targets != 1 && n_targets != n) return set_error(LIFEB200_E_ARG, "target count must be 1 (broadcast) or n");
+  contains_shifted_kernel<<<grid_warps(n), kBlockC, 0, ctx->stream>>>(states, n, targets, n_targets, dx, dy, contains);
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+int lifeb200_contains_target_batch_host(lifeb200_ctx* ctx, const uint64_t* states, size_t n, const uint64_t* targets,
+                                        size_t n_targets, int dx, int dy, uint8_t* contains) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (!states || !targets || !contains) return set_error(LIFEB200_E_ARG, "null pointer");
+  if (n_targets != 1 && n_targets != n) return set_error(LIFEB200_E_ARG, "target count must be 1 (broadcast) or n");
+  // item = state (512 B) for a shared target, state + its target (1536 B staged side by side) otherwise
+  if (n_targets == 1) {
+    if (int rc = ensure_scratch(ctx->d_tabbuf, ctx->tabbuf_cap, 2 * LIFEB200_PATTERN_BYTES)) return rc;
+    ctx->tab_valid = false;  // the table scratch is reused: the enumeration's cached tables are gone
+    LIFEB200_CUDA(cudaMemcpyAsync(ctx->d_tabbuf, targets, 2 * LIFEB200_PATTERN_BYTES, cudaMemcpyHostToDevice, ctx->stream));
+    LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+    const uint64_t* d_t = static_cast<const uint64_t*>(ctx->d_tabbuf);
+    return host_pipeline_impl(ctx, states, contains, n, LIFEB200_PATTERN_BYTES, 1, true, (size_t)1 << 16,
+                              [&](cudaStream_t st, const uint64_t* din, uint64_t* dout, size_t cnt) -> int {
+                                contains_shifted_kernel<<<grid_warps(cnt), kBlockC, 0, st>>>(din, cnt, d_t, 1, dx, dy,
+                                                                                             reinterpret_cast<uint8_t*>(dout));
+                                LIFEB200_LAUNCHED(ctx);
+                                return LIFEB200_OK;
+                              });
+  }
+  const size_t chunk = std::min<size_t>(n, (size_t)1 << 15);
+  const size_t nchunks = (n + chunk - 1) / chunk;
+  const int used = (int)std::min<size_t>(kSlots, nchunks);
+  for (int s = 0; s < used; s++)
+    if (int rc = ensure_slot(ctx, s, chunk * 3 * LIFEB200_PATTERN_BYTES, chunk)) return rc;
+  auto body = [&]() -> int {
+    for (size_t c = 0; c < nchunks; c++) {
+      Slot& sl = ctx->slots[c % kSlots];
+      const size_t off = c * chunk, cnt = std::min(chunk, n - off);
+      uint64_t* d_s = static_cast<uint64_t*>(sl.dbuf);
+      uint64_t* d_t = d_s + chunk * kN;
+      LIFEB200_CUDA(cudaMemcpyAsync(d_s, states + off * kN, cnt * LIFEB200_PATTERN_BYTES, cudaMemcpyHostToDevice, sl.stream));
+      LIFEB200_CUDA(cudaMemcpyAsync(d_t, targets + off * 2 * kN, cnt * 2 * LIFEB200_PATTERN_BYTES, cudaMemcpyHostToDevice, sl.stream));
+      contains_shifted_kernel<<<grid_warps(cnt), kBlockC, 0, sl.stream>>>(d_s, cnt, d_t, cnt, dx, dy, static_cast<uint8_t*>(sl.dbuf2));
+      LIFEB200_LAUNCHED(ctx);
+      LIFEB200_CUDA(cudaMemcpyAsync(contains + off, sl.dbuf2, cnt, cudaMemcpyDeviceToHost, sl.stream));
+    }
+    for (int s = 0; s < used; s++) LIFEB200_CUDA(cudaStreamSynchronize(ctx->slots[s].stream));
+    return LIFEB200_OK;
+  };
+  const int rc = body();
+  if (rc) drain_slots(ctx, used);
+  return rc;
 }
 
 }  // extern "C"

@@ -738,6 +738,35 @@ int lifeb200_step_match_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const u
   return compact_hits(ctx, n, first_id, hits, cap, n_hits);
 }
 
+// Host form of the call above: patterns, targets, the optional index and the hit records are HOST arrays; hits come
+// back in id order.  One upload, one launch, one compaction, one download of the records that were found.
+int lifeb200_step_match_host(lifeb200_ctx* ctx, const uint64_t* patterns, const uint64_t* targets,
+                             const uint32_t* target_index, size_t n, size_t n_targets, uint64_t first_id, unsigned gens,
+                             unsigned stable_interval, lifeb200_hit* hits, size_t cap, uint64_t* n_hits) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n_hits) *n_hits = 0;
+  if (stable_interval == 0) return set_error(LIFEB200_E_ARG, "stable_interval must be >= 1");
+  if (n == 0) return LIFEB200_OK;
+  if (!patterns || !targets || n_targets == 0 || (!hits && cap)) return set_error(LIFEB200_E_ARG, "null pointer");
+  const size_t pat_b = n * LIFEB200_PATTERN_BYTES, tgt_b = n_targets * 2 * LIFEB200_PATTERN_BYTES;
+  const size_t idx_b = target_index ? ((n * sizeof(uint32_t) + 15) & ~(size_t)15) : 0;
+  if (int rc = ensure_slot(ctx, 0, pat_b + tgt_b + idx_b, 0)) return rc;
+  if (int rc = ensure_scratch(ctx->d_hitbuf, ctx->hitbuf_cap, std::max<size_t>(cap, 1) * sizeof(lifeb200_hit))) return rc;
+  char* d = static_cast<char*>(ctx->slots[0].dbuf);
+  LIFEB200_CUDA(cudaMemcpyAsync(d, patterns, pat_b, cudaMemcpyHostToDevice, ctx->stream));
+  LIFEB200_CUDA(cudaMemcpyAsync(d + pat_b, targets, tgt_b, cudaMemcpyHostToDevice, ctx->stream));
+  if (target_index)
+    LIFEB200_CUDA(cudaMemcpyAsync(d + pat_b + tgt_b, target_index, n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+  lifeb200_hit* d_hits = static_cast<lifeb200_hit*>(ctx->d_hitbuf);
+  int rc = lifeb200_step_match_dev(ctx, reinterpret_cast<const uint64_t*>(d), reinterpret_cast<const uint64_t*>(d + pat_b),
+                                   target_index ? reinterpret_cast<const uint32_t*>(d + pat_b + tgt_b) : nullptr, n, first_id,
+                                   gens, stable_interval, d_hits, cap, ctx->d_counters + 0);
+  if (rc) { cudaStreamSynchronize(ctx->stream); return rc; }
+  LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+  LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+  return download_hits(ctx, d_hits, cap, hits, n_hits);
+}
+
 static int enumerate_args(const uint64_t* catalysts, unsigned n_catalysts, const uint64_t* projectiles,
                           unsigned n_projectiles, uint64_t id_begin, uint64_t* id_end, unsigned stable_interval,
                           const lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* n_skipped, bool* empty) {

@@ -8,6 +8,7 @@
 //       lifeapi_b200/_lib/liblifeapi_b200.so oracle/_build/liblifeoracle.so
 #include <cstdio>
 #include <random>
+#include <sstream>
 #include <vector>
 
 #include "LifeAPI_b200.hpp"
@@ -243,7 +244,60 @@ static void Locate_And_RLE() {
   EXPECT_TRUE(checked > 200);
 }
 
+// Call sites of the reference that the round-1 header did not compile: RandomState, InitializedTag,
+// operator<<, Move(pair), Cell, shifted Contains, CountNeighbours / StepFor, Parse of an RLE with a header line.
+static void Reference_CallSites() {
+  PRNG::Seed(12345);
+  const LifeState a = LifeState::RandomState();
+  PRNG::Seed(12345);
+  EXPECT_EQ(a, LifeState::RandomState());  // seedable
+  uint64_t all_or = 0, all_and = ~0ULL;
+  for (int i = 0; i < N; i++) { all_or |= a[i]; all_and &= a[i]; }
+  EXPECT_EQ(all_or >> 62, 0ULL);           // LifeAPI.hpp:21-22: draws in [2^61, 2^62] -> bits 63, 62 clear, bit 61 set
+  EXPECT_EQ((all_and >> 61) & 1ULL, 1ULL);
+  LifeState u(InitializedTag::UNINITIALIZED);
+  u = a;
+  EXPECT_EQ(u, a);
+  LifeState m = a;
+  m.Move(std::make_pair(3, -5));
+  EXPECT_EQ(m, a.Moved(3, -5));
+  EXPECT_EQ(m, a.Moved(std::make_pair(3, 59)));
+  EXPECT_EQ(LifeState::Cell({7, 9}).GetPop(), 1u);
+  EXPECT_TRUE(LifeState::Cell({7, 9}).Get(7, 9));
+  std::ostringstream os;
+  os << a;
+  EXPECT_EQ(os.str(), a.RLE());
+  // StepFor / CountNeighbours (LifeAPI.hpp:889-895,1042-1064) agree with the GPU Step on every cell of a soup
+  const LifeState next = a.Stepped();
+  int bad = 0;
+  for (int x = 0; x < N; x++)
+    for (int y = 0; y < N; y++) {
+      bad += a.StepFor({x, y}) != next.Get((unsigned)x, (unsigned)y);
+      bad += a.CountNeighbours({x, y}) + (a.Get({x, y}) ? 1u : 0u) != a.CountNeighboursWithCenter({x, y});
+    }
+  EXPECT_EQ(bad, 0);
+  // shifted Contains (LifeTarget.hpp:38-42): a target built at the origin is found at the offset its pattern was moved by
+  const LifeState eater = LifeState::Parse("2b2o$bobo$bo$2o!");
+  const LifeTarget t(eater);
+  for (int dx : {0, 1, 31, 63})
+    for (int dy : {0, 5, 62}) {
+      const LifeState s = eater.Moved(dx, dy);
+      EXPECT_TRUE(s.Contains(t, dx, dy));
+      EXPECT_TRUE(!s.Contains(t, dx + 1, dy));
+      EXPECT_EQ(s.Contains(t, dx, dy), s.Contains(t.Moved({dx, dy})));
+      EXPECT_TRUE(s.Contains(eater, dx, dy) && s.AreDisjoint(t.unwanted, dx, dy));
+    }
+  // Parse follows GenericParse (Parsing.hpp:141-190): the header line is dropped, so RLEWHeader round-trips
+  LifeHistory h;
+  h.state = eater;
+  EXPECT_EQ(LifeHistory::Parse(h.RLEWHeader()).state, eater.Moved(32, 32));
+  EXPECT_EQ(LifeState::Parse("x = 4, y = 4, rule = B3/S23\n2b2o$bobo$bo$2o!"), eater);
+  EXPECT_EQ(LifeState::Parse("2b2o$bobo$bo$2o!", 3, 4), eater.Moved(3, 4));
+  EXPECT_EQ(LifeState::Parse("2A!").GetPop(), 0u);  // only 'o' sets a cell in the two-state alphabet
+}
+
 int main() {
+  Reference_CallSites();
   Locate_And_RLE();
   Weld_Hash_Interaction();
   Stable_And_History();

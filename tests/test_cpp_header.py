@@ -23,6 +23,55 @@ def build_binary():
     return BIN
 
 
+REF_TEST = "/root/reference/tests/StepAltTest.cpp"
+REF_BIN = os.path.join(ROOT, "tests", "cpp", "_build", "reference_StepAltTest")
+
+
+def build_reference_test():
+    """The reference's OWN tests/StepAltTest.cpp, body verbatim: the file is read where it lies and piped to g++
+    with only its `#include "../LifeAPI.hpp"` line pointed at the drop-in header (nothing is copied into the repo);
+    <gtest/gtest.h> resolves to tests/cpp/gtest_shim.  Built only where /root/reference exists; the binary travels
+    to the GPU box in tests/cpp/_build/ like the other prebuilt checkers."""
+    from lifeapi_b200.build import build
+    so = build()
+    if not os.path.exists(REF_TEST):
+        return REF_BIN if os.path.exists(REF_BIN) else None
+    os.makedirs(os.path.dirname(REF_BIN), exist_ok=True)
+    hdr = os.path.join(ROOT, "include", "LifeAPI_b200.hpp")
+    shim = os.path.join(ROOT, "tests", "cpp", "gtest_shim")
+    if not os.path.exists(REF_BIN) or os.path.getmtime(REF_BIN) < max(os.path.getmtime(p) for p in (
+            REF_TEST, so, hdr, os.path.join(shim, "gtest", "gtest.h"))):
+        text = open(REF_TEST).read()
+        assert '#include "../LifeAPI.hpp"' in text
+        text = text.replace('#include "../LifeAPI.hpp"', '#include "LifeAPI_b200.hpp"')
+        subprocess.run(["g++", "-std=c++20", "-O2", "-Wall", "-Wextra", "-I" + os.path.join(ROOT, "include"),
+                        "-I" + shim, "-o", REF_BIN, "-x", "c++", "-", "-x", "none", so, "-Wl,-rpath," + os.path.dirname(so)], input=text, text=True, check=True)
+    return REF_BIN
+
+
+def test_reference_own_step_alt_test_compiles_against_the_drop_in_header():
+    if not os.path.exists(REF_TEST):
+        pytest.skip("needs /root/reference (the binary is prebuilt for the GPU box)")
+    import torch
+    exe = build_reference_test()
+    assert exe and os.path.exists(exe)
+    if not torch.cuda.is_available():
+        r = subprocess.run([exe], capture_output=True, text=True)
+        assert r.returncode != 0 and "lifeb200_create" in r.stderr  # no GPU: abort, never a silent CPU path
+
+
+@pytest.mark.gpu
+def test_reference_own_step_alt_test_passes_on_gpu():
+    """tests/StepAltTest.cpp:5-13 verbatim: 10000 RandomState soups, Step() == StepAlt() -- here two different GPU
+    circuits (the step kernel's pair-shared select against the interaction kernel's two-full-adder form)."""
+    exe = build_reference_test()
+    if exe is None:
+        pytest.skip("tests/cpp/_build/reference_StepAltTest was not prebuilt (needs /root/reference at build time)")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "all passed" in r.stdout and "StepAltTest.Random" in r.stdout
+
+
 def test_header_compiles_and_fails_loudly_without_gpu():
     import torch
     exe = build_binary()
