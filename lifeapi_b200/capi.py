@@ -502,6 +502,64 @@ class Engine:
         return self._roundtrip(patterns, (n, 4, WORDS), np.uint64,
                                lambda di, do: self._check(self.lib.lifeb200_interaction_counts_dev(self._h, di, do, n)))
 
+    def weld_step_batch_host(self, records: np.ndarray, gens: int) -> np.ndarray:
+        rec = np.ascontiguousarray(records, dtype=np.uint64).copy()
+        self._check(self.lib.lifeb200_weld_step_batch_host(self._h, _ptr(rec), rec.size // (4 * WORDS), gens))
+        return rec
+
+    def history_step_batch_host(self, records: np.ndarray, gens: int) -> np.ndarray:
+        rec = np.ascontiguousarray(records, dtype=np.uint64).copy()
+        self._check(self.lib.lifeb200_history_step_batch_host(self._h, _ptr(rec), rec.size // (4 * WORDS), gens))
+        return rec
+
+    def interaction_counts_host(self, patterns: np.ndarray) -> np.ndarray:
+        patterns = np.ascontiguousarray(patterns, dtype=np.uint64)
+        n = patterns.size // WORDS
+        out = np.empty((n, 4, WORDS), dtype=np.uint64)
+        self._check(self.lib.lifeb200_interaction_counts_host(self._h, _ptr(patterns), _ptr(out), n))
+        return out
+
+    def stable_vulnerable_host(self, records: np.ndarray) -> np.ndarray:
+        records = np.ascontiguousarray(records, dtype=np.uint64)
+        n = records.size // STABLE_WORDS
+        out = np.empty((n, WORDS), dtype=np.uint64)
+        self._check(self.lib.lifeb200_stable_vulnerable_host(self._h, _ptr(records), _ptr(out), n))
+        return out
+
+    def unknown_step_refined_host(self, records: np.ndarray, current_on: np.ndarray, current_unknown: np.ndarray, variant: int = 0):
+        records = np.ascontiguousarray(records, dtype=np.uint64)
+        current_on = np.ascontiguousarray(current_on, dtype=np.uint64)
+        current_unknown = np.ascontiguousarray(current_unknown, dtype=np.uint64)
+        n = records.size // STABLE_WORDS
+        outs = [np.empty((n, WORDS), dtype=np.uint64) for _ in range(3)]
+        self._check(self.lib.lifeb200_unknown_step_refined_host(self._h, _ptr(records), _ptr(current_on), _ptr(current_unknown), n,
+                                                                variant, _ptr(outs[0]), _ptr(outs[1]), _ptr(outs[2])))
+        return tuple(outs)
+
+    def step_match_host(self, patterns: np.ndarray, targets: np.ndarray, target_index: np.ndarray | None, gens: int,
+                        stable_interval: int, first_id: int = 0, cap: int | None = None) -> np.ndarray:
+        patterns = np.ascontiguousarray(patterns, dtype=np.uint64)
+        targets = np.ascontiguousarray(targets, dtype=np.uint64)
+        n, nt = patterns.size // WORDS, targets.size // (2 * WORDS)
+        cap = n if cap is None else cap
+        if target_index is not None:
+            target_index = np.ascontiguousarray(target_index, dtype=np.uint32)
+        hits = np.zeros(max(cap, 1), dtype=HIT_DTYPE)
+        nh = C.c_uint64()
+        self._check(self.lib.lifeb200_step_match_host(self._h, _ptr(patterns), _ptr(targets), _ptr(target_index), n, nt, first_id,
+                                                      gens, stable_interval, _ptr(hits), cap, C.byref(nh)))
+        return hits[: nh.value].copy()
+
+    def contains_target_batch_host(self, states: np.ndarray, targets: np.ndarray, dx: int, dy: int) -> np.ndarray:
+        """LifeState::Contains(const LifeTarget&, dx, dy) for every state; targets: one (2, 64) record or one per state."""
+        (states, n), (targets, nt) = self._planes(states), self._planes(targets, 2 * WORDS)
+        out = np.zeros(n, dtype=np.uint8)
+        self._check(self.lib.lifeb200_contains_target_batch_host(self._h, _ptr(states), n, _ptr(targets), nt, dx, dy, _ptr(out)))
+        return out.astype(bool)
+
+    def contains_target_batch_dev(self, d_states, n: int, d_targets, n_targets: int, dx: int, dy: int, d_out) -> None:
+        self._check(self.lib.lifeb200_contains_target_batch_dev(self._h, _ptr(d_states), n, _ptr(d_targets), n_targets, dx, dy, _ptr(d_out)))
+
     def hash_batch_dev(self, d_patterns, d_hashes, n: int) -> None:
         self._check(self.lib.lifeb200_hash_batch_dev(self._h, _ptr(d_patterns), _ptr(d_hashes), n))
 
