@@ -156,6 +156,54 @@ def config4_enumeration(eng, p_int):
     return out
 
 
+def step_match_explicit(eng, p_int):
+    """The explicit-pattern API (lifeb200_step_match_dev): 256 Ki placements built on the host as catalyst | glider.Moved,
+    one LifeTarget per catalyst, 256 generations; 4 patterns per lane group (step_match_kernel_x) against the
+    lane-group kernel (layout 2 pinned)."""
+    names = list(STILL_LIFES)
+    cats = np.stack([_pattern(STILL_LIFES[names[i % 8]], 28, 28, D4[(i // 8) * 2]) for i in range(32)])
+    n, gens, interval = 1 << 18, 256, 8
+    rng = np.random.default_rng(4)
+    c_idx = rng.integers(0, 32, size=n)
+    gl = np.stack([_pattern(GLIDER, int(x), int(y), D4[int(t)]) for x, y, t in zip(rng.integers(0, 64, 512), rng.integers(0, 64, 512), rng.integers(0, 8, 512))])
+    pats = cats[c_idx] | gl[rng.integers(0, 512, size=n)]
+    tg = np.zeros((32, 2, 64), dtype=np.uint64)
+    for c in range(32):
+        z = np.zeros(64, dtype=np.uint64)
+        for dx in (-1, 0, 1):
+            col = np.roll(cats[c], dx)
+            z |= col | (col << np.uint64(1)) | (col >> np.uint64(63)) | (col >> np.uint64(1)) | (col << np.uint64(63))
+        tg[c, 0], tg[c, 1] = cats[c], z & ~cats[c]
+    d_p, d_t, d_i, d_h, d_n = eng.malloc(pats.nbytes), eng.malloc(tg.nbytes), eng.malloc(n * 4), eng.malloc(n * 16), eng.malloc(8)
+    try:
+        eng.h2d(d_p, np.ascontiguousarray(pats))
+        eng.h2d(d_t, tg)
+        eng.h2d(d_i, c_idx.astype(np.uint32))
+        eng.sync()
+        out = {"workload": f"step_match_dev: {n} explicit placements x <= {gens} gens, one LifeTarget per catalyst, stable_interval {interval}"}
+        res = {}
+        for name, layout in (("four_per_group", 0), ("lane_group_layout2", 2)):
+            eng.set_step_layout(layout)
+            try:
+                ms = _time(eng, lambda: eng.step_match_dev(d_p, d_t, d_i, n, 0, gens, interval, d_h, n, d_n))
+                cnt = np.zeros(1, dtype=np.uint64)
+                eng.d2h(cnt, d_n)
+                eng.sync()
+                hits = np.zeros(int(cnt[0]), dtype=[("id", "<u8"), ("a", "<u4"), ("b", "<u4")])
+                if len(hits):
+                    eng.d2h(hits, d_h)
+                    eng.sync()
+                res[name] = hits
+                out[name] = {"ms": ms, "placements_per_s": n / (ms * 1e-3), "hits": int(cnt[0])}
+            finally:
+                eng.set_step_layout(0)
+        out["kernels_agree"] = bool(res["four_per_group"].tobytes() == res["lane_group_layout2"].tobytes())
+        return out
+    finally:
+        for p in (d_p, d_t, d_i, d_h, d_n):
+            eng.free(p)
+
+
 def config5_survey(eng, p_int):
     """Soups generated on device, 4096 gens, activity test + hit compaction (1/16 of the 16 Mi-soup config per call)."""
     n, gens = 1 << 20, 4096
@@ -372,7 +420,7 @@ def _d2d(eng, dst, src, nbytes):
 
 def run_extras(eng, p_int):
     out = {}
-    for name, fn in (("config3", config3_unknown_step), ("config4", config4_enumeration), ("config5", config5_survey),
+    for name, fn in (("config3", config3_unknown_step), ("config4", config4_enumeration), ("step_match", step_match_explicit), ("config5", config5_survey),
                      ("stable_propagate", stable_propagate), ("next_rows", next_rows), ("locate", locate_rows)):
         try:
             out[name] = fn(eng, p_int)

@@ -546,3 +546,64 @@ class LifeBatch {
   void* d_ = nullptr;
   size_t n_ = 0, cap_ = 0;
 };
+
+// ---------------------------------------------------------------------------------------------
+// Multi-GPU batches (SURVEY.md 8b "init with device list", "multi-GPU run + gather"; 8e): a group of GPUs in this
+// process, every call sharded by contiguous id range, hit lists gathered over NCCL into this process, sorted by id.
+// The reference is single-threaded; this is the loop a caller shards (LifeAPI.hpp:877-881) done by the library.
+// ---------------------------------------------------------------------------------------------
+class LifeMultiBatch {
+ public:
+  // the first n_devices GPUs (0 = every visible GPU), or an explicit device list
+  explicit LifeMultiBatch(int n_devices = 0) { lifeb200::Check(lifeb200_multi_create(nullptr, n_devices, &m_), "lifeb200_multi_create"); }
+  explicit LifeMultiBatch(const std::vector<int>& devices) {
+    lifeb200::Check(lifeb200_multi_create(devices.data(), (int)devices.size(), &m_), "lifeb200_multi_create");
+  }
+  ~LifeMultiBatch() { lifeb200_multi_destroy(m_); }
+  LifeMultiBatch(const LifeMultiBatch&) = delete;
+  LifeMultiBatch& operator=(const LifeMultiBatch&) = delete;
+
+  int World() const { int w = 0; lifeb200_multi_info(m_, &w, nullptr, nullptr, nullptr); return w; }
+  int NcclVersion() const { int v = 0; lifeb200_multi_info(m_, nullptr, nullptr, nullptr, &v); return v; }
+  float LastGatherMs() const { float ms = 0; lifeb200_multi_last_gather_ms(m_, &ms); return ms; }
+  lifeb200_ctx* Context(int local_index) const { lifeb200_ctx* c = nullptr; lifeb200::Check(lifeb200_multi_ctx(m_, local_index, &c), "lifeb200_multi_ctx"); return c; }
+
+  // batch[i].Step(gens) for every i, the batch split over the GPUs (one host thread and one copy pipeline per GPU)
+  void Step(std::vector<LifeState>& batch, unsigned gens) {
+    if (batch.empty()) return;
+    lifeb200::Check(lifeb200_multi_step_batch_host(m_, batch[0].state, batch[0].state, batch.size(), gens), "LifeMultiBatch::Step");
+  }
+  // config 5: on-device soups, active iff state(G) != state(G - 2); returns the number of hits (hits resized to fit)
+  size_t SoupSurvey(uint64_t first_id, uint64_t n, uint64_t seed, int dist, unsigned gens, std::vector<LifeHit>& hits,
+                    uint64_t* pop_sum = nullptr, uint64_t* hash_xor = nullptr) {
+    if (hits.size() < 4096) hits.resize(4096);
+    for (;;) {
+      uint64_t nh = 0;
+      const int rc = lifeb200_multi_soup_survey(m_, first_id, n, seed, dist, gens, reinterpret_cast<lifeb200_hit*>(hits.data()),
+                                                hits.size(), &nh, pop_sum, hash_xor);
+      if (rc == LIFEB200_E_OVERFLOW) { hits.resize(nh); continue; }
+      lifeb200::Check(rc, "LifeMultiBatch::SoupSurvey");
+      return (size_t)nh;
+    }
+  }
+  // config 4 over the group; hits sorted by placement id
+  std::vector<LifeHit> EnumerateCollisions(const std::vector<LifeState>& catalysts, const std::vector<LifeState>& projectiles,
+                                           unsigned gens, unsigned stable_interval, uint64_t* n_skipped = nullptr) {
+    const uint64_t total = (uint64_t)catalysts.size() * projectiles.size() * 4096ull;
+    std::vector<LifeHit> hits(4096);
+    for (;;) {
+      uint64_t nh = 0, ns = 0;
+      const int rc = lifeb200_multi_enumerate_collisions(m_, catalysts[0].state, (unsigned)catalysts.size(), projectiles[0].state,
+                                                         (unsigned)projectiles.size(), 0, total, gens, stable_interval,
+                                                         reinterpret_cast<lifeb200_hit*>(hits.data()), hits.size(), &nh, &ns);
+      if (rc == LIFEB200_E_OVERFLOW) { hits.resize(nh); continue; }
+      lifeb200::Check(rc, "LifeMultiBatch::EnumerateCollisions");
+      hits.resize(nh);
+      if (n_skipped) *n_skipped = ns;
+      return hits;
+    }
+  }
+
+ private:
+  lifeb200_multi* m_ = nullptr;
+};

@@ -282,6 +282,42 @@ __device__ __forceinline__ uint32_t group8_or(uint32_t v) {
   return v;
 }
 
+// The generation loop of the layout-8 match kernels: 4 patterns per group of 8 lanes; `planes` points at this lane's
+// column of the group's parked target planes ([32 words][8 lanes] uint4: words 0..15 wanted, 16..31 mask), `mine`
+// = which of the four patterns this lane keeps the recovery state machine of.
+__device__ __forceinline__ void run_match_x(TileX<8>& t, const uint4* planes, int sub, int mine, unsigned gens,
+                                            unsigned stable_interval, Recovery& r) {
+  // The group-wide OR and the recovery state machine of generation g - 1 sit at the top of iteration g, in
+  // the same basic block as the step, so their shuffle latency hides under it (two warps per scheduler:
+  // nothing else would cover it); the first call sees d_prev = 0 and changes nothing.  The per-register
+  // differences are OR-ed as a tree, not a 32-deep chain.
+  uint32_t d_prev = 0;
+#pragma unroll 1
+  for (unsigned g = 1; g <= gens; g++) {
+    asm volatile("" ::: "memory");  // keep the shared loads inside the loop (hoisted they are 128 registers)
+    const uint32_t all = group8_or(d_prev);  // bit 4j+q set: some cell of placement q differed after g - 1
+    r.observe_flat((all & (0x11111111u << mine)) != 0, g - 1, stable_interval);
+    t.step(sub);
+    uint32_t dc[8];
+#pragma unroll
+    for (int col = 0; col < 8; col++) {
+      const uint4 wa = planes[(2 * col) * 8], wb = planes[(2 * col + 1) * 8];
+      const uint4 ma = planes[(16 + 2 * col) * 8], mb = planes[(17 + 2 * col) * 8];
+      const uint32_t x0 = lop3<kAndXor>(t.r[col][0], ma.x, wa.x), x1 = lop3<kAndXor>(t.r[col][1], ma.y, wa.y);
+      const uint32_t x2 = lop3<kAndXor>(t.r[col][2], ma.z, wa.z), x3 = lop3<kAndXor>(t.r[col][3], ma.w, wa.w);
+      const uint32_t x4 = lop3<kAndXor>(t.r[col][4], mb.x, wb.x), x5 = lop3<kAndXor>(t.r[col][5], mb.y, wb.y);
+      const uint32_t x6 = lop3<kAndXor>(t.r[col][6], mb.z, wb.z), x7 = lop3<kAndXor>(t.r[col][7], mb.w, wb.w);
+      dc[col] = lop3<kOr3>(lop3<kOr3>(x0, x1, x2), lop3<kOr3>(x3, x4, x5), x6 | x7);
+    }
+    d_prev = lop3<kOr3>(lop3<kOr3>(dc[0], dc[1], dc[2]), lop3<kOr3>(dc[3], dc[4], dc[5]), dc[6] | dc[7]);
+    if ((g & 7u) == 0 && __all_sync(0xffffffffu, r.done)) break;  // decided up to g - 1: nothing left to observe
+  }
+  {
+    const uint32_t all = group8_or(d_prev);
+    r.observe_flat((all & (0x11111111u << mine)) != 0, gens, stable_interval);
+  }
+}
+
 __global__ void __launch_bounds__(128, 1) enumerate_kernel_x(const uint64_t* __restrict__ cat_zoi,
                                                              const uint64_t* __restrict__ proj,
                                                              const uint64_t* __restrict__ proj_zoi,
@@ -367,36 +403,71 @@ __global__ void __launch_bounds__(128, 1) enumerate_kernel_x(const uint64_t* __r
     unsigned sk = __ballot_sync(0xffffffffu, valid && skip && sub < P);
     if (lane == 0 && sk) atomicAdd(n_skipped, (unsigned long long)__popc(sk));
   }
-  // The group-wide OR and the recovery state machine of generation g - 1 sit at the top of iteration g, in
-  // the same basic block as the step, so their shuffle latency hides under it (two warps per scheduler:
-  // nothing else would cover it); the first call sees d_prev = 0 and changes nothing.  The per-register
-  // differences are OR-ed as a tree, not a 32-deep chain.
-  uint32_t d_prev = 0;
-#pragma unroll 1
-  for (unsigned g = 1; g <= gens; g++) {
-    asm volatile("" ::: "memory");  // keep the shared loads inside the loop (hoisted they are 128 registers)
-    const uint32_t all = group8_or(d_prev);  // bit 4j+q set: some cell of placement q differed after g - 1
-    r.observe_flat((all & (0x11111111u << mine)) != 0, g - 1, stable_interval);
-    t.step(sub);
-    uint32_t dc[8];
-#pragma unroll
-    for (int col = 0; col < 8; col++) {
-      const uint4 wa = planes[(2 * col) * 8], wb = planes[(2 * col + 1) * 8];
-      const uint4 ma = planes[(16 + 2 * col) * 8], mb = planes[(17 + 2 * col) * 8];
-      const uint32_t x0 = lop3<kAndXor>(t.r[col][0], ma.x, wa.x), x1 = lop3<kAndXor>(t.r[col][1], ma.y, wa.y);
-      const uint32_t x2 = lop3<kAndXor>(t.r[col][2], ma.z, wa.z), x3 = lop3<kAndXor>(t.r[col][3], ma.w, wa.w);
-      const uint32_t x4 = lop3<kAndXor>(t.r[col][4], mb.x, wb.x), x5 = lop3<kAndXor>(t.r[col][5], mb.y, wb.y);
-      const uint32_t x6 = lop3<kAndXor>(t.r[col][6], mb.z, wb.z), x7 = lop3<kAndXor>(t.r[col][7], mb.w, wb.w);
-      dc[col] = lop3<kOr3>(lop3<kOr3>(x0, x1, x2), lop3<kOr3>(x3, x4, x5), x6 | x7);
-    }
-    d_prev = lop3<kOr3>(lop3<kOr3>(dc[0], dc[1], dc[2]), lop3<kOr3>(dc[3], dc[4], dc[5]), dc[6] | dc[7]);
-    if ((g & 7u) == 0 && __all_sync(0xffffffffu, r.done)) break;  // decided up to g - 1: nothing left to observe
-  }
-  {
-    const uint32_t all = group8_or(d_prev);
-    r.observe_flat((all & (0x11111111u << mine)) != 0, gens, stable_interval);
-  }
+  run_match_x(t, planes, sub, mine, gens, stable_interval, r);
   if (valid && sub < P) dense[id - id_begin] = dense_record(r.hit, r.first_false, r.recovered);
+}
+
+// The explicit-pattern match (lifeb200_step_match_*) with 4 patterns per group of 8 lanes: patterns p0 .. p0 + 3 are
+// packed bit-interleaved (layout 8) and so are THEIR targets -- every pattern has its own, so the group packs the four
+// wanted planes and the four wanted | unwanted planes on the device and parks them in its own 4 KiB slice of shared
+// memory.  Same loop as the enumeration: 7.75 + 1.5 integer-pipe instructions per register and generation instead
+// of the 8.5 + 1.5 of step_match_kernel (layout 2).
+__global__ void __launch_bounds__(128, 1) step_match_kernel_x(const uint64_t* __restrict__ patterns,
+                                                              const uint64_t* __restrict__ targets,
+                                                              const uint32_t* __restrict__ target_index, size_t n,
+                                                              unsigned gens, unsigned stable_interval,
+                                                              uint64_t* __restrict__ dense) {
+  constexpr int M = 8, P = 4;
+  const size_t gid = (size_t)blockIdx.x * 128 + threadIdx.x;
+  const size_t p0 = (gid >> 3) * P;
+  const int sub = threadIdx.x & 7, mine = sub & 3;
+  const size_t p = p0 + mine;
+  const bool valid = p < n;
+  extern __shared__ uint4 parked[];  // [16 groups][32 words][8 lanes]; words 0..15 wanted, 16..31 mask
+  uint4* slice = parked + (threadIdx.x >> 3) * 256 + sub;
+  const uint64_t* tg[P];
+#pragma unroll
+  for (int q = 0; q < P; q++)
+    tg[q] = (p0 + q < n) ? targets + (size_t)(target_index ? target_index[p0 + q] : 0u) * 2 * kN : nullptr;
+  TileX<M> t;
+#pragma unroll
+  for (int pl = 0; pl < 3; pl++) {  // 0: wanted, 1: wanted | unwanted, 2: the patterns themselves
+#pragma unroll
+    for (int c = 0; c < 8; c += 2) {
+      uint64_t wa[P], wb[P];
+#pragma unroll
+      for (int q = 0; q < P; q++) {
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (p0 + q < n) {
+          if (pl == 2) {
+            v = __ldg(reinterpret_cast<const uint4*>(patterns + (p0 + q) * kN + sub * 8 + c));
+          } else {
+            v = __ldg(reinterpret_cast<const uint4*>(tg[q] + sub * 8 + c));
+            if (pl == 1) {
+              const uint4 u = __ldg(reinterpret_cast<const uint4*>(tg[q] + kN + sub * 8 + c));
+              v.x |= u.x; v.y |= u.y; v.z |= u.z; v.w |= u.w;
+            }
+          }
+        }
+        wa[q] = ((uint64_t)v.y << 32) | v.x;
+        wb[q] = ((uint64_t)v.w << 32) | v.z;
+      }
+      t.pack(c, wa);
+      t.pack(c + 1, wb);
+      if (pl < 2) {
+#pragma unroll
+        for (int cc = c; cc < c + 2; cc++) {
+          slice[(pl * 16 + 2 * cc) * 8] = make_uint4(t.r[cc][0], t.r[cc][1], t.r[cc][2], t.r[cc][3]);
+          slice[(pl * 16 + 2 * cc + 1) * 8] = make_uint4(t.r[cc][4], t.r[cc][5], t.r[cc][6], t.r[cc][7]);
+        }
+      }
+    }
+  }
+  __syncwarp();
+  Recovery r;
+  if (!valid) r.done = true;
+  run_match_x(t, slice, sub, mine, gens, stable_interval, r);
+  if (valid && sub < P) dense[p] = dense_record(r.hit, r.first_false, r.recovered);
 }
 
 // Per-pattern 64-bit fold used as a size-independent checksum (build-defined):
@@ -558,7 +629,7 @@ static void host_zoi(const uint64_t* s, uint64_t* out) {  // LifeAPI.hpp:521-536
 // match kernels keep three tiles (state, wanted&mask, mask) in registers: cap W at 16.
 // packing 4 placements costs about 6 generations of stepping
 // measured crossovers against the lane-group kernels (profiles/r01z_multi_thresholds.txt)
-constexpr unsigned kEnumerateMultiFrom = 16, kSurveyMultiFrom = 16;
+constexpr unsigned kEnumerateMultiFrom = 16, kSurveyMultiFrom = 16, kStepMatchMultiFrom = 32;
 static inline int match_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
 static inline int survey_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
 
@@ -731,9 +802,19 @@ int lifeb200_step_match_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const u
   if (!aligned16(patterns) || !aligned16(targets)) return set_error(LIFEB200_E_ARG, "pointers must be 16-byte aligned");
   if (int rc = ensure_dense(ctx, n)) return rc;
   uint64_t* dense = static_cast<uint64_t*>(ctx->d_dense);
-  int lpp = match_lpp(ctx);
-  LIFEB200_DISPATCH_LPP_MIN4(lpp, (step_match_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
-                                      patterns, targets, target_index, n, gens, stable_interval, dense)));
+  // many generations: 4 patterns per lane group in the row-class layout (step_match_kernel_x), unless the caller
+  // pinned the lane grouping or another layout; packing three planes of four patterns costs about 10 generations
+  const bool multi = ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kStepMatchMultiFrom));
+  if (multi) {
+    const size_t groups = (n + 3) / 4;
+    LIFEB200_CUDA(cudaFuncSetAttribute(step_match_kernel_x, cudaFuncAttributeMaxDynamicSharedMemorySize, kEnumXSmem));
+    step_match_kernel_x<<<(unsigned)((groups * 8 + 127) / 128), 128, kEnumXSmem, ctx->stream>>>(
+        patterns, targets, target_index, n, gens, stable_interval, dense);
+  } else {
+    int lpp = match_lpp(ctx);
+    LIFEB200_DISPATCH_LPP_MIN4(lpp, (step_match_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
+                                        patterns, targets, target_index, n, gens, stable_interval, dense)));
+  }
   LIFEB200_LAUNCHED(ctx);
   return compact_hits(ctx, n, first_id, hits, cap, n_hits);
 }

@@ -7,6 +7,7 @@
 #include "ctx.h"
 #include "host_pipeline.cuh"
 #include "life_core.cuh"
+#include "life_multi.cuh"
 #include "xxh3_keys.h"
 
 namespace lifeb200 {
@@ -42,6 +43,113 @@ __global__ void __launch_bounds__(kBlockN, 1) weld_step_kernel(uint64_t* __restr
     }
   }
   if (valid) s.store(records + p * 4 * kN, sub);
+}
+
+// ---- LifeWeld::Step in the row-class layout (life_multi.cuh): 4 records per group of 8 lanes ----------------
+// The state lives in registers exactly as in step_kernel_x<8> (64 registers per lane, 1/4 shift per register and
+// generation).  The three frozen planes are constants of the launch and do not fit beside it (64 + 192), so every
+// lane packs them once and parks them in shared memory (768 B per lane, [48][128] uint4 per CTA: a warp's LDS.128
+// reads 32 consecutive uint4, conflict-free) and reads them back every generation: 48 LDS.128 against ~980 integer
+// instructions.  Per 32 cells and generation: 2 LOP3 column count + 1/4 SHF + 13 LOP3 =
+//   s0, k0 = full adder of the three low count bits; s1, k1 = of the three high ones        (sum = s0 + 2 (k0 + s1) + 4 k1)
+//   T0 = s0 ^ f0, c0 = s0 & f0; x = k0 ^ s1; T1 = x ^ f1 ^ c0, c1 = maj(x, f1, c0); S2 = k1 ^ (k0 & s1); T2 = S2 ^ f2 ^ c1
+//   next = (T0 ^ T2) & (cell | T0) & (T1 ^ T2)          -- bit3 of the count and the last carry dropped, as the reference does
+// A warp whose 16 records have no frozen cell at all (LifeWeld(state), LifeWeld.hpp:24-25) runs the plain step.
+constexpr int kWeldXSmem = 128 * 48 * 16;
+constexpr int kWeldU = 0x38;  // (a ^ b) & (c | a) with a = 0xF0, b = 0xCC, c = 0xAA
+
+__device__ __forceinline__ uint32_t weld_rule(uint32_t l0, uint32_t l1, uint32_t m0, uint32_t m1, uint32_t r0, uint32_t r1,
+                                              uint32_t cell, uint32_t f2, uint32_t f1, uint32_t f0) {
+  const uint32_t s0 = lop3<kXor3>(l0, m0, r0), k0 = lop3<kMaj>(l0, m0, r0);
+  const uint32_t s1 = lop3<kXor3>(l1, m1, r1), k1 = lop3<kMaj>(l1, m1, r1);
+  const uint32_t t0 = s0 ^ f0, c0 = s0 & f0;
+  const uint32_t x = k0 ^ s1;
+  const uint32_t t1 = lop3<kXor3>(x, f1, c0), c1 = lop3<kMaj>(x, f1, c0);
+  const uint32_t s2 = lop3<kXorAnd>(k1, k0, s1);
+  const uint32_t t2 = lop3<kXor3>(s2, f2, c1);
+  const uint32_t u = lop3<kWeldU>(t0, t2, cell);  // (t0 ^ t2) & (cell | t0)
+  return lop3<kXorThenAnd>(t1, t2, u);           // (t1 ^ t2) & u
+}
+
+__global__ void __launch_bounds__(128, 2) weld_step_kernel_x(uint64_t* records, size_t n, unsigned gens) {
+  constexpr int M = 8, P = 4;
+  using TX = TileX<M>;
+  const size_t gid = (size_t)blockIdx.x * 128 + threadIdx.x;
+  const size_t p0 = (gid >> 3) * P;
+  const int sub = threadIdx.x & 7;
+  extern __shared__ uint4 frozen[];  // [48][128]: plane pl, column c, half h at row pl * 16 + c * 2 + h
+  TX t;
+  uint32_t any = 0;
+#pragma unroll
+  for (int pl = 0; pl < 4; pl++) {
+#pragma unroll
+    for (int c = 0; c < 8; c += 2) {
+      uint64_t wa[P], wb[P];
+#pragma unroll
+      for (int q = 0; q < P; q++) {
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (p0 + q < n) v = *reinterpret_cast<const uint4*>(records + (p0 + q) * 4 * kN + pl * kN + sub * 8 + c);
+        wa[q] = ((uint64_t)v.y << 32) | v.x;
+        wb[q] = ((uint64_t)v.w << 32) | v.z;
+      }
+      if (pl == 0) {
+        t.pack(c, wa);
+        t.pack(c + 1, wb);
+      } else {
+        TX tmp;  // only columns c, c + 1 are touched: two columns' worth of registers
+        tmp.pack(c, wa);
+        tmp.pack(c + 1, wb);
+#pragma unroll
+        for (int cc = c; cc < c + 2; cc++) {
+          frozen[((pl - 1) * 16 + cc * 2) * 128 + threadIdx.x] = make_uint4(tmp.r[cc][0], tmp.r[cc][1], tmp.r[cc][2], tmp.r[cc][3]);
+          frozen[((pl - 1) * 16 + cc * 2 + 1) * 128 + threadIdx.x] = make_uint4(tmp.r[cc][4], tmp.r[cc][5], tmp.r[cc][6], tmp.r[cc][7]);
+#pragma unroll
+          for (int k = 0; k < M; k++) any |= tmp.r[cc][k];
+        }
+      }
+    }
+  }
+  const bool warp_frozen = __any_sync(0xffffffffu, any != 0);  // uniform over the warp: no divergence below
+  if (!warp_frozen) {
+#pragma unroll 1
+    for (unsigned g = 0; g < gens; g++) t.step(sub);
+  } else {
+#pragma unroll 1
+    for (unsigned g = 0; g < gens; g++) {
+      asm volatile("" ::: "memory");  // keep the shared loads inside the loop (hoisted they are 192 registers)
+      const TX::Col first = t.count(0), last = t.count(7);
+      TX::Col prev = TX::halo(last, sub + 7);
+      const TX::Col after = TX::halo(first, sub + 1);
+      TX::Col cur = first;
+#pragma unroll
+      for (int c = 0; c < 8; c++) {
+        const TX::Col next = (c == 7) ? after : (c + 1 == 7) ? last : t.count(c + 1);
+        uint32_t f[3][M];
+#pragma unroll
+        for (int pl = 0; pl < 3; pl++) {
+          const uint4 a = frozen[(pl * 16 + c * 2) * 128 + threadIdx.x], b = frozen[(pl * 16 + c * 2 + 1) * 128 + threadIdx.x];
+          f[pl][0] = a.x; f[pl][1] = a.y; f[pl][2] = a.z; f[pl][3] = a.w;
+          f[pl][4] = b.x; f[pl][5] = b.y; f[pl][6] = b.z; f[pl][7] = b.w;
+        }
+#pragma unroll
+        for (int k = 0; k < M; k++)
+          t.r[c][k] = weld_rule(prev.b0[k], prev.b1[k], cur.b0[k], cur.b1[k], next.b0[k], next.b1[k], t.r[c][k], f[0][k], f[1][k], f[2][k]);
+        prev = cur;
+        cur = next;
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    uint64_t wa[P], wb[P];
+    t.unpack(c, wa);
+    t.unpack(c + 1, wb);
+#pragma unroll
+    for (int q = 0; q < P; q++)
+      if (p0 + q < n)
+        *reinterpret_cast<uint4*>(records + (p0 + q) * 4 * kN + sub * 8 + c) =
+            make_uint4((uint32_t)wa[q], (uint32_t)(wa[q] >> 32), (uint32_t)wb[q], (uint32_t)(wb[q] >> 32));
+  }
 }
 
 // ---- InteractionCounts[AndNext]: out1, out2, outMore (+ next), the reference's formulas verbatim ----
@@ -191,7 +299,16 @@ static unsigned grid_hash(const lifeb200_ctx* ctx, size_t n) {
 
 extern "C" {
 
+// packing four planes of four records costs about 23 generations of the cheaper loop (5 x 12.5 instructions per register against 2.75 saved per generation)
+constexpr unsigned kWeldMultiFrom = 24;
 static int launch_weld(lifeb200_ctx* ctx, cudaStream_t st, uint64_t* records, size_t n, unsigned gens) {
+  if (ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kWeldMultiFrom))) {
+    const size_t groups = (n + 3) / 4;
+    LIFEB200_CUDA(cudaFuncSetAttribute(weld_step_kernel_x, cudaFuncAttributeMaxDynamicSharedMemorySize, kWeldXSmem));
+    weld_step_kernel_x<<<(unsigned)((groups * 8 + 127) / 128), 128, kWeldXSmem, st>>>(records, n, gens);
+    LIFEB200_LAUNCHED(ctx);
+    return LIFEB200_OK;
+  }
   int lpp = std::max(8, effective_lpp(ctx));  // 8 tiles live: keep W <= 8
   LIFEB200_DISPATCH_LPP_MIN4(lpp, (weld_step_kernel<LPP><<<grid_n(n, LPP), kBlockN, 0, st>>>(records, n, gens)));
   LIFEB200_LAUNCHED(ctx);

@@ -23,6 +23,34 @@ def build_binary():
     return BIN
 
 
+MULTI_BIN = os.path.join(ROOT, "tests", "cpp", "_build", "multi_survey")
+
+
+def build_multi_survey():
+    from lifeapi_b200.build import build
+    so = build()
+    src = os.path.join(ROOT, "tests", "cpp", "multi_survey.cpp")
+    os.makedirs(os.path.dirname(MULTI_BIN), exist_ok=True)
+    if not os.path.exists(MULTI_BIN) or os.path.getmtime(MULTI_BIN) < max(os.path.getmtime(p) for p in (
+            src, so, os.path.join(ROOT, "include", "LifeAPI_b200.hpp"))):
+        subprocess.run(["g++", "-std=c++20", "-O2", "-Wall", "-Wextra", "-I" + os.path.join(ROOT, "include"), src, "-o", MULTI_BIN,
+                        so, "-Wl,-rpath," + os.path.dirname(so)], check=True)
+    return MULTI_BIN
+
+
+def test_multi_gpu_cpp_program_builds():
+    assert os.path.exists(build_multi_survey())
+
+
+@pytest.mark.gpu
+def test_multi_gpu_cpp_program_matches_single_gpu():
+    """A C++ program (no Python in the data path) surveys soups on every visible GPU through lifeb200_multi_* and gets
+    the byte-identical hit list a single context returns; on a one-GPU box the group has one rank."""
+    r = subprocess.run([build_multi_survey(), str(200003), "300"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "identical" in r.stdout and "all passed" in r.stdout
+
+
 REF_TEST = "/root/reference/tests/StepAltTest.cpp"
 REF_BIN = os.path.join(ROOT, "tests", "cpp", "_build", "reference_StepAltTest")
 

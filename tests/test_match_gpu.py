@@ -30,18 +30,22 @@ def test_step_match_vs_oracle(engine, port):
     rng.shuffle(ids)
     pats, tidx = placements(port, c, ids)
     n = len(ids)
-    for lpp, gens, interval in ((4, 128, 8), (8, 160, 6), (32, 90, 3)):
+    # lanes pinned -> step_match_kernel (layout 2); default / layout 8 -> step_match_kernel_x (4 patterns per lane
+    # group, per-pattern targets packed on the device)
+    for lpp, layout, gens, interval in ((4, 0, 128, 8), (8, 0, 160, 6), (32, 0, 90, 3), (0, 0, 128, 8), (0, 8, 20, 3), (0, 2, 128, 8)):
         engine.set_lanes_per_pattern(lpp)
+        engine.set_step_layout(layout)
         try:
             hits = engine.step_match(pats, targets, tidx, gens=gens, stable_interval=interval, first_id=1000)
         finally:
             engine.set_lanes_per_pattern(0)
+            engine.set_step_layout(0)
         want = []
         for p in range(n):
             r = port.step_match(pats[p], targets[tidx[p]], gens, interval)
             if r:
                 want.append((1000 + p, r[0], r[1]))
-        assert len(want) > 100
+        assert len(want) > (100 if gens > 50 else 0)
         assert [(int(h["id"]), int(h["g_first_false"]), int(h["g_recovered"])) for h in hits] == want, lpp
 
 
@@ -62,6 +66,9 @@ def test_step_match_single_target_and_overflow(engine, port):
         engine.step_match(pats, tgt[None], None, 128, 0)
     assert ei.value.code == E_ARG
     assert len(engine.step_match(pats[:0], tgt[None], None, 10, 2)) == 0
+    for n in (1, 2, 3, 5, 7):  # ragged around the 4-pattern group of step_match_kernel_x
+        got = engine.step_match(pats[:n], tgt[None], None, 128, 8)
+        assert list(got["id"]) == [k for k in range(n) if port.step_match(pats[k], tgt, 128, 8)]
 
 
 def test_enumeration_vs_reference_golden(engine):

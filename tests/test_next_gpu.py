@@ -69,3 +69,33 @@ def test_weld_and_interaction_vs_oracle(engine, port, lpp):
         assert (engine.interaction_counts(s)[:, 3] == port.step_batch(s, 1)).all()
     finally:
         engine.set_lanes_per_pattern(0)
+
+
+def test_weld_step_every_kernel_vs_reference(engine, ref, port):
+    """LifeWeld::Step through both kernels -- 4 records per lane group in the row-class layout (default from 24
+    generations, or layout 8 pinned) and the lane-group kernel (layout 1 / pinned lanes) -- on dense frozen planes
+    (every carry of the 3-bit add exercised), on sparse ones, and on records with no frozen cell (the plain-step
+    fast path); ragged batch sizes around the 4-record group."""
+    raw = port.soup(77, 4 * 1030, SEED, 0).reshape(1030, 4, 64)
+    dense = raw.copy()
+    sparse = raw.copy()
+    sparse[:, 1] &= sparse[:, 2] & sparse[:, 3] & ~sparse[:, 0]
+    sparse[:, 2] &= sparse[:, 3] & ~sparse[:, 0]
+    sparse[:, 3] &= ~sparse[:, 0]
+    plain = raw.copy()
+    plain[:, 1:] = 0
+    mixed = sparse.copy()
+    mixed[::3, 1:] = 0  # warps with and without frozen cells side by side
+    for name, recs in (("dense", dense), ("sparse", sparse), ("plain", plain), ("mixed", mixed)):
+        for n in (1, 3, 4, 5, 1030):
+            for layout, lpp, gens in ((0, 0, 40), (8, 0, 3), (1, 0, 40), (0, 16, 25)):
+                engine.set_step_layout(layout)
+                engine.set_lanes_per_pattern(lpp)
+                try:
+                    got = engine.weld_step_batch(recs[:n], gens)
+                finally:
+                    engine.set_step_layout(0)
+                    engine.set_lanes_per_pattern(0)
+                want = ref.weld_step_batch(recs[:n], gens, 0)
+                assert (got == want).all(), (name, n, layout, lpp, gens)
+    assert (engine.weld_step_batch(plain[:64], 30)[:, 0] == port.step_batch(plain[:64, 0], 30)).all()  # frozen = 0 is Step

@@ -1,0 +1,156 @@
+"""Exact synthesis of a single-output 3-input-LUT network for a named specification (CNF, solved by `z3 -dimacs`).
+
+    python tools/lut_synth_generic_cnf.py <spec> <gates> [--timeout S]
+
+A specification is a list of named input columns over its CARE rows plus the wanted output column; the solver
+looks for `gates` LOP3 gates, each reading three earlier signals (inputs or gates), the last gate being the
+output.  Same SSV-style encoding as tools/lut_synth_pair_cnf.py (selection variables one-hot per operand,
+ordered operands to break symmetry, normal gates: lut[0] = 0 except for the output gate).
+
+Specs
+  weld_tail   the part of LifeWeld::Step (LifeWeld.hpp:169-186) after the two full adders over the column counts:
+              inputs s0, k0, s1, k1 (3x3 sum = s0 + 2 (k0 + s1) + 4 k1, centre included), cell, f0, f1, f2;
+              output (T0 ^ T2) & (T1 ^ T2) & (cell | T0) with T = (sum + f) mod 8.  Rows: every (left, mid, right)
+              column-count triple in 0..3 with cell <= [mid >= 1] and mid == 3 => cell, every f in 0..7.
+              csrc/next.cu uses 9 gates for it.
+"""
+import itertools
+import subprocess
+import sys
+import tempfile
+import time
+
+
+def spec_weld_tail():
+    rows = []
+    for l, m, r in itertools.product(range(4), repeat=3):
+        for cell in (0, 1):
+            if cell and m < 1:
+                continue
+            if m == 3 and not cell:
+                continue
+            l0, l1, m0, m1, r0, r1 = l & 1, l >> 1, m & 1, m >> 1, r & 1, r >> 1
+            s0, k0 = l0 ^ m0 ^ r0, int(l0 + m0 + r0 >= 2)
+            s1, k1 = l1 ^ m1 ^ r1, int(l1 + m1 + r1 >= 2)
+            total = l + m + r
+            assert total == s0 + 2 * (k0 + s1) + 4 * k1
+            for f in range(8):
+                t = (total + f) & 7
+                out = int(t == 3 or (t == 4 and cell))
+                rows.append(((s0, k0, s1, k1, cell, f & 1, (f >> 1) & 1, f >> 2), out))
+    uniq = {}
+    for ins, out in rows:
+        assert uniq.setdefault(ins, out) == out, "inconsistent care rows"
+    names = ["s0", "k0", "s1", "k1", "cell", "f0", "f1", "f2"]
+    return names, sorted(uniq.items())
+
+
+SPECS = {"weld_tail": spec_weld_tail}
+
+
+class Cnf:
+    def __init__(self):
+        self.n = 0
+        self.clauses = []
+
+    def var(self):
+        self.n += 1
+        return self.n
+
+    def add(self, *lits):
+        self.clauses.append(lits)
+
+    def exactly_one(self, xs):
+        self.add(*xs)
+        for a, b in itertools.combinations(xs, 2):
+            self.add(-a, -b)
+
+
+def build(names, rows, gates):
+    cnf = Cnf()
+    n_in, n_rows = len(names), len(rows)
+    sig = [[("c", rows[r][0][i]) for r in range(n_rows)] for i in range(n_in)]  # per signal: per-row constant or variable
+    meta = []
+    for g in range(gates):
+        m = len(sig)
+        sel = [[cnf.var() for _ in range(m)] for _ in range(3)]
+        for k in range(3):
+            cnf.exactly_one(sel[k])
+        for k in range(2):  # operand k+1 strictly after operand k
+            for i in range(m):
+                for j in range(0, i + 1):
+                    cnf.add(-sel[k][i], -sel[k + 1][j])
+        if g > 0:  # every gate but the first must be used later or be the output: weak pruning, skip
+            pass
+        lut = [cnf.var() for _ in range(8)]
+        last = g == gates - 1
+        if not last:
+            cnf.add(-lut[0])
+        out = [cnf.var() for _ in range(n_rows)]
+        for r in range(n_rows):
+            x = [cnf.var() for _ in range(3)]
+            for k in range(3):
+                for i in range(m):
+                    kind, v = sig[i][r]
+                    if kind == "c":
+                        cnf.add(-sel[k][i], x[k] if v else -x[k])
+                    else:
+                        cnf.add(-sel[k][i], -x[k], v)
+                        cnf.add(-sel[k][i], x[k], -v)
+            for idx in range(8):
+                bits = [(idx >> 2) & 1, (idx >> 1) & 1, idx & 1]
+                pre = [(-x[k] if bits[k] else x[k]) for k in range(3)]
+                cnf.add(*pre, -lut[idx], out[r])
+                cnf.add(*pre, lut[idx], -out[r])
+            if last:
+                cnf.add(out[r] if rows[r][1] else -out[r])
+        sig.append([("v", out[r]) for r in range(n_rows)])
+        meta.append((sel, lut))
+    return cnf, meta
+
+
+def solve(cnf, timeout):
+    with tempfile.NamedTemporaryFile("w", suffix=".cnf", delete=False) as f:
+        f.write(f"p cnf {cnf.n} {len(cnf.clauses)}\n")
+        for c in cnf.clauses:
+            f.write(" ".join(map(str, c)) + " 0\n")
+        path = f.name
+    t0 = time.time()
+    try:
+        out = subprocess.run(["z3", "-dimacs", f"-T:{timeout}", path], capture_output=True, text=True, timeout=timeout + 60).stdout
+    except subprocess.TimeoutExpired:
+        return "timeout", None, time.time() - t0
+    dt = time.time() - t0
+    if out.startswith("s SATISFIABLE") or out.startswith("sat"):
+        model = set()
+        for line in out.split("\n"):
+            if line.startswith("v "):
+                model.update(int(t) for t in line[2:].split() if int(t) > 0)
+            elif line and line[0] in "-0123456789":
+                model.update(int(t) for t in line.split() if int(t) > 0)
+        return "sat", model, dt
+    if "UNSAT" in out.upper():
+        return "unsat", None, dt
+    return "unknown/timeout", None, dt
+
+
+def main():
+    spec, gates = sys.argv[1], int(sys.argv[2])
+    timeout = int(sys.argv[sys.argv.index("--timeout") + 1]) if "--timeout" in sys.argv else 3600
+    names, rows = SPECS[spec]()
+    cnf, meta = build(names, rows, gates)
+    print(f"{spec}: {len(names)} inputs, {len(rows)} care rows, {gates} gates -> {cnf.n} vars, {len(cnf.clauses)} clauses", flush=True)
+    status, model, dt = solve(cnf, timeout)
+    print(f"{spec} gates={gates}: {status} in {dt:.0f} s", flush=True)
+    if status == "sat":
+        labels = list(names)
+        for g, (sel, lut) in enumerate(meta):
+            ops = [labels[[i for i, v in enumerate(sel[k]) if v in model][0]] for k in range(3)]
+            tt = sum(1 << idx for idx in range(8) if lut[idx] in model)
+            # LOP3 immediate convention: a = 0xF0, b = 0xCC, c = 0xAA -> bit (a<<2 | b<<1 | c)
+            print(f"  g{g} = lop3<0x{tt:02X}>({ops[0]}, {ops[1]}, {ops[2]})")
+            labels.append(f"g{g}")
+
+
+if __name__ == "__main__":
+    main()
