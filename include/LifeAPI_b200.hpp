@@ -401,6 +401,11 @@ struct LifeWeld {
     lifeb200::Check(lifeb200_weld_step_batch_host(lifeb200::DefaultContext(), state.state, 1, numIters), "LifeWeld::Step");
   }
   LifeTarget ToTarget() const;  // LifeWeld.hpp:188-191 (defined after LifeTarget)
+  void InteractionCounts(LifeState& out1, LifeState& out2, LifeState& outMore) const {  // LifeWeld.hpp:193-215
+    alignas(64) uint64_t planes[3 * N];
+    lifeb200::Check(lifeb200_weld_interaction_counts_host(lifeb200::DefaultContext(), state.state, planes, 1), "LifeWeld::InteractionCounts");
+    std::memcpy(out1.state, planes, 512); std::memcpy(out2.state, planes + N, 512); std::memcpy(outMore.state, planes + 2 * N, 512);
+  }
 };
 static_assert(sizeof(LifeWeld) == 2048, "LifeWeld layout (LifeWeld.hpp:18-22)");
 inline LifeTarget LifeWeld::ToTarget() const {

@@ -97,6 +97,14 @@ int lifeb200_soup_dev(lifeb200_ctx* ctx, uint64_t* out, uint64_t first_id, size_
 int lifeb200_neighbour_count_dev(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n);
 int lifeb200_neighbour_count_host(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n);
 
+/* NeighbourCount arithmetic on batches of count records (NeighbourCount.hpp:71-102; a record = bit3, bit2, bit1, bit0
+ * = 2048 B, as the constructor above writes them): out[p] = a[p].Add(b[p], incarry[p]) -- a 4-stage ripple with a
+ * carry-in plane (n x 512 B; NULL = the empty plane, i.e. operator+), carry-out discarded; Subtract(o) = Add(~o,
+ * all-ones) (operator-); WithExactly(k) = AND of the planes, negated where k has a 0 bit (out: n x 512 B). */
+int lifeb200_nc_add_dev(lifeb200_ctx* ctx, const uint64_t* a, const uint64_t* b, const uint64_t* incarry, uint64_t* out, size_t n);
+int lifeb200_nc_subtract_dev(lifeb200_ctx* ctx, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n);
+int lifeb200_nc_with_exactly_dev(lifeb200_ctx* ctx, const uint64_t* counts, unsigned k, uint64_t* out, size_t n);
+
 /* ---- A11/A12  fused step + LifeState::Contains(const LifeTarget&) (LifeTarget.hpp:44-51) - */
 typedef struct lifeb200_hit {
   uint64_t id;             /* pattern / placement id */
@@ -240,6 +248,10 @@ int lifeb200_weld_step_batch_host(lifeb200_ctx* ctx, uint64_t* records, size_t n
  * InteractionCounts, :956-995): planes[p] = out1, out2, outMore, next (4 x 512 B). */
 int lifeb200_interaction_counts_dev(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n);
 int lifeb200_interaction_counts_host(lifeb200_ctx* ctx, const uint64_t* in, uint64_t* planes, size_t n);
+/* LifeWeld::InteractionCounts (LifeWeld.hpp:193-215): InteractionCounts of the record's state with every plane
+ * masked by the zone of influence of its NON-frozen cells; planes[p] = out1, out2, outMore (3 x 512 B). */
+int lifeb200_weld_interaction_counts_dev(lifeb200_ctx* ctx, const uint64_t* records, uint64_t* planes, size_t n);
+int lifeb200_weld_interaction_counts_host(lifeb200_ctx* ctx, const uint64_t* records, uint64_t* planes, size_t n);
 /* LifeState::GetHash (LifeAPI.hpp:373) = XXH3_64bits(state, 512) with the default secret
  * (xxHash v0.8.3, the reference's vendored submodule): hashes[p] for p < n. */
 int lifeb200_hash_batch_dev(lifeb200_ctx* ctx, const uint64_t* patterns, uint64_t* hashes, size_t n);

@@ -85,6 +85,11 @@ SIGNATURES = {
     "lifeb200_unknown_step_refined_host": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp, _vp]),
     "lifeb200_weld_step_batch_host": (C.c_int, [_vp, _vp, C.c_size_t, C.c_uint]),
     "lifeb200_interaction_counts_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_nc_add_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_nc_subtract_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_nc_with_exactly_dev": (C.c_int, [_vp, _vp, C.c_uint, _vp, C.c_size_t]),
+    "lifeb200_weld_interaction_counts_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "lifeb200_weld_interaction_counts_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "lifeb200_enumerate_collisions": (C.c_int, [_vp, _vp, C.c_uint, _vp, C.c_uint, C.c_uint64, C.c_uint64, C.c_uint,
                                                 C.c_uint, _vp, C.c_size_t, _u64p, _u64p]),
     "lifeb200_soup_survey": (C.c_int, [_vp, C.c_uint64, C.c_size_t, C.c_uint64, C.c_int, C.c_uint, _vp, C.c_size_t,
@@ -559,6 +564,42 @@ class Engine:
 
     def contains_target_batch_dev(self, d_states, n: int, d_targets, n_targets: int, dx: int, dy: int, d_out) -> None:
         self._check(self.lib.lifeb200_contains_target_batch_dev(self._h, _ptr(d_states), n, _ptr(d_targets), n_targets, dx, dy, _ptr(d_out)))
+
+    def weld_interaction_counts_host(self, records: np.ndarray) -> np.ndarray:
+        records = np.ascontiguousarray(records, dtype=np.uint64)
+        n = records.size // (4 * WORDS)
+        out = np.empty((n, 3, WORDS), dtype=np.uint64)
+        self._check(self.lib.lifeb200_weld_interaction_counts_host(self._h, _ptr(records), _ptr(out), n))
+        return out
+
+    def nc_arith(self, op: str, a: np.ndarray, b: np.ndarray | None = None, incarry: np.ndarray | None = None, k: int = 0) -> np.ndarray:
+        """NeighbourCount batch arithmetic through the *_dev entry points: op in add / subtract / with_exactly."""
+        a = np.ascontiguousarray(a, dtype=np.uint64)
+        n = a.size // (4 * WORDS)
+        out = np.empty((n, WORDS) if op == "with_exactly" else (n, 4, WORDS), dtype=np.uint64)
+        bufs = {"a": self.malloc(max(a.nbytes, 16)), "o": self.malloc(max(out.nbytes, 16))}
+        try:
+            self.h2d(bufs["a"], a)
+            for name, arr in (("b", b), ("c", incarry)):
+                if arr is not None:
+                    arr = np.ascontiguousarray(arr, dtype=np.uint64)
+                    bufs[name] = self.malloc(max(arr.nbytes, 16))
+                    self.h2d(bufs[name], arr)
+            if op == "add":
+                self._check(self.lib.lifeb200_nc_add_dev(self._h, bufs["a"], bufs["b"], bufs.get("c"), bufs["o"], n))
+            elif op == "subtract":
+                self._check(self.lib.lifeb200_nc_subtract_dev(self._h, bufs["a"], bufs["b"], bufs["o"], n))
+            elif op == "with_exactly":
+                self._check(self.lib.lifeb200_nc_with_exactly_dev(self._h, bufs["a"], k, bufs["o"], n))
+            else:
+                raise ValueError(op)
+            if out.nbytes:
+                self.d2h(out, bufs["o"])
+            self.sync()
+        finally:
+            for p in bufs.values():
+                self.free(p)
+        return out
 
     def hash_batch_dev(self, d_patterns, d_hashes, n: int) -> None:
         self._check(self.lib.lifeb200_hash_batch_dev(self._h, _ptr(d_patterns), _ptr(d_hashes), n))

@@ -118,3 +118,39 @@ def test_partial_overlap_rejected_and_in_place_allowed(engine, port):
         assert ei.value.code == E_ARG
     finally:
         engine.free(d)
+
+
+def test_neighbour_count_arithmetic_batches_vs_reference(engine, ref, port):
+    """NeighbourCount::Add / operator+ / Subtract / WithExactly (NeighbourCount.hpp:71-102) on batches: real count
+    records (0..9 per cell) and arbitrary planes (every carry pattern), with and without a carry-in plane."""
+    n = 777
+    soups = port.soup(11, 2 * n, SEED, 0)
+    ca, cb = engine.neighbour_count_host(soups[:n]), engine.neighbour_count_host(soups[n:])
+    ra, rb = port.soup(5000, 4 * n, SEED, 0).reshape(n, 4, 64), port.soup(9000, 4 * n, SEED, 0).reshape(n, 4, 64)
+    carry = port.soup(123, n, SEED, 0)
+    for a, b in ((ca, cb), (ra, rb)):
+        assert (engine.nc_arith("add", a, b) == ref.nc_add_batch(a, b)).all()
+        assert (engine.nc_arith("add", a, b, incarry=carry) == ref.nc_add_batch(a, b, carry)).all()
+        assert (engine.nc_arith("subtract", a, b) == ref.nc_subtract_batch(a, b)).all()
+        for k in (0, 3, 4, 9, 15):
+            assert (engine.nc_arith("with_exactly", a, k=k) == ref.nc_with_exactly_batch(a, k)).all(), k
+    z = engine.nc_arith("subtract", ca, ca)
+    assert not z.any()  # x - x == 0 on every plane
+    assert engine.nc_arith("add", ca[:0], cb[:0]).size == 0
+
+
+def test_weld_interaction_counts_vs_reference(engine, ref, port):
+    """LifeWeld::InteractionCounts (LifeWeld.hpp:193-215): welded still lifes (some cells frozen) and dense random records."""
+    n = 515
+    raw = port.soup(31, 4 * n, SEED, 0).reshape(n, 4, 64)
+    recs = raw.copy()
+    recs[:, 0] &= raw[:, 1] & raw[:, 2]          # sparser states: isolated cells and small clumps, real interaction counts
+    recs[:, 1] &= recs[:, 0] & raw[:, 3]         # a share of the live cells is frozen ...
+    recs[:, 2] = np.roll(recs[:, 1], 1, axis=0) & ~recs[:, 0]   # ... and some dead ones carry frozen counts too
+    recs[:, 3] &= raw[:, 2] & raw[:, 1]
+    for r in (recs, raw):
+        assert (engine.weld_interaction_counts_host(r) == ref.weld_interaction_counts_batch(r, 0)).all()
+    plain = recs.copy()
+    plain[:, 1:] = 0  # no frozen cells: LifeState::InteractionCounts masked by the state's own ZOI (a no-op on these planes)
+    got = engine.weld_interaction_counts_host(plain)
+    assert (got == engine.interaction_counts_host(plain[:, 0])[:, :3]).all()
