@@ -662,6 +662,20 @@ class Engine:
         return out
 
 
+def _prefer_bundled_nccl() -> None:
+    """If this interpreter has a pip-bundled NCCL (nvidia-nccl-cu12, what torch links), point the library at that file
+    unless the caller chose one: a process must not end up with two different libnccl.so.2 (the first one loaded wins
+    the soname, and a later `import torch` against an older system NCCL fails on missing symbols).  No torch import."""
+    import sys
+    if os.environ.get("LIFEB200_NCCL_LIB"):
+        return
+    for base in sys.path:
+        cand = os.path.join(base, "nvidia", "nccl", "lib", "libnccl.so.2")
+        if os.path.exists(cand):
+            os.environ["LIFEB200_NCCL_LIB"] = cand
+            return
+
+
 class MultiEngine:
     """A multi-GPU group (lifeb200_multi_*): every rank in this process (devices=[...]) or one rank per process
     (rank / world / unique_id, the id made by MultiEngine.unique_id() on rank 0 and distributed by the caller)."""
@@ -670,6 +684,7 @@ class MultiEngine:
                  unique_id: bytes | None = None):
         self.lib = load_library()
         self._h = None
+        _prefer_bundled_nccl()
         h = _vp()
         if rank is None:
             arr = None
@@ -686,6 +701,7 @@ class MultiEngine:
     @staticmethod
     def unique_id() -> bytes:
         lib = load_library()
+        _prefer_bundled_nccl()
         buf = C.create_string_buffer(UNIQUE_ID_BYTES)
         _lib_check(lib, lib.lifeb200_multi_unique_id(buf))
         return buf.raw

@@ -27,7 +27,7 @@ int main(int argc, char** argv) {
   const uint64_t seed = 0x4C696665415049ull;
 
   LifeMultiBatch group(want_gpus);  // lifeb200_multi_create over the first want_gpus devices (0: every visible one)
-  std::vector<LifeHit> hits;
+  std::vector<LifeHit> hits(n / 8 + 4096);  // room for one hit in eight ids: a list that does not fit costs a second full run
   uint64_t pop_sum = 0, hash_xor = 0;
   group.SoupSurvey(0, 4096 * (uint64_t)group.World(), seed, 0, 16, hits, &pop_sum, &hash_xor);  // warm-up: NCCL channels, scratch
   const auto t0 = std::chrono::steady_clock::now();

@@ -184,7 +184,7 @@ def test_multi_one_process_per_gpu(engine):
     receives the merged list over NCCL, every rank the counters."""
     if _device_count() < 2:
         pytest.skip("needs two GPUs")
-    import torch.multiprocessing as mp
+    import multiprocessing as mp
     from lifeapi_b200 import MultiEngine
     uid = MultiEngine.unique_id()
     first, n, gens = 1000, 5001, 64
