@@ -20,6 +20,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -136,6 +137,13 @@ static int for_each_device(lifeb200_multi* m, F fn) {
 // rank; on rank 0, hits[0 .. total) = the whole list in id order.
 static int gather_body(lifeb200_multi* m, lifeb200_hit* hits, size_t cap, uint64_t* counters) {
   const int world = m->world, k = m->n_local();
+  static const bool trace = std::getenv("LIFEB200_TRACE_GATHER") != nullptr;  // host-side timestamps of the steps below
+  const auto t_begin = std::chrono::steady_clock::now();
+  auto stamp = [&](const char* what) {
+    if (trace)
+      std::fprintf(stderr, "[lifeb200 gather rank %d] %-28s +%.3f ms\n", m->first_rank, what,
+                   std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count());
+  };
   std::vector<unsigned long long> all((size_t)world * 4, 0);
   lifeb200_ctx* c0 = m->ctx[0];
   if (k == world) {
@@ -165,6 +173,7 @@ static int gather_body(lifeb200_multi* m, lifeb200_hit* hits, size_t cap, uint64
     counters[3] ^= all[(size_t)r * 4 + 3];
   }
   counters[0] = total;
+  stamp("counts known");
   if (total > cap) return set_error(LIFEB200_E_OVERFLOW, "hit buffer too small: %llu hits, capacity %llu",
                                     (unsigned long long)total, (unsigned long long)cap);
   if (total == 0) return LIFEB200_OK;
@@ -182,6 +191,7 @@ static int gather_body(lifeb200_multi* m, lifeb200_hit* hits, size_t cap, uint64
       if (int rc = ensure_scratch(m->d_gather, m->gather_cap, total * sizeof(lifeb200_hit))) return rc;
     }
     char* root_buf = static_cast<char*>(m->d_gather);
+    stamp("gather buffer ready");
     LIFEB200_NCCL(g_nccl.GroupStart());
     for (int i = 0; i < k; i++) {
       const int r = m->first_rank + i;
@@ -195,6 +205,7 @@ static int gather_body(lifeb200_multi* m, lifeb200_hit* hits, size_t cap, uint64
       }
     }
     LIFEB200_NCCL(g_nccl.GroupEnd());
+    stamp("send / recv enqueued");
     if (m->owns_root()) {
       LIFEB200_CUDA(cudaSetDevice(c0->device));
       if (cnt[0])
@@ -202,10 +213,12 @@ static int gather_body(lifeb200_multi* m, lifeb200_hit* hits, size_t cap, uint64
       LIFEB200_CUDA(cudaMemcpyAsync(hits, root_buf, total * sizeof(lifeb200_hit), cudaMemcpyDeviceToHost, c0->stream));
     }
   }
+  stamp("download enqueued");
   for (int i = 0; i < k; i++) {
     LIFEB200_CUDA(cudaSetDevice(m->ctx[i]->device));
     LIFEB200_CUDA(cudaStreamSynchronize(m->ctx[i]->stream));
   }
+  stamp("streams drained");
   return LIFEB200_OK;
 }
 
