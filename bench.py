@@ -372,7 +372,7 @@ def main():
         try:
             cap5 = total5
             h_hits = np.zeros(cap5 if rank == 0 else 1, dtype=HIT_DTYPE)
-            group.soup_survey(0, min(total5, world << 12), SEED, 0, 16, cap5, hits=h_hits)  # untimed: NCCL channel set-up, scratch
+            group.soup_survey(0, total5, SEED, 0, 2, cap5, hits=h_hits)  # untimed: kernel image, scratch and gather buffers at their final size
             barrier()
             t0 = time.perf_counter()
             merged, ps5, hx5 = group.soup_survey(0, total5, SEED, 0, gens5, cap5, hits=h_hits)

@@ -94,8 +94,6 @@ struct lifeb200_multi {
   std::vector<ncclComm_t> comm;     // one communicator per local device (empty when world == 1)
   std::vector<void*> d_allc;        // per local device: world x 4 u64 gathered counters
   unsigned long long* h_allc = nullptr;  // pinned: world x 4 u64
-  void* d_gather = nullptr;         // rank 0's device: concatenated hit lists
-  size_t gather_cap = 0;
   int gather_mode = 0;              // 0 = NCCL send/recv to rank 0's GPU, one download; 1 = every local GPU downloads
                                     //     its list straight into the caller's buffer (single-process groups only)
   float last_gather_ms = 0.f;
@@ -186,12 +184,11 @@ static int gather_body(lifeb200_multi* m, lifeb200_hit* hits, size_t cap, uint64
                                     m->ctx[i]->stream));
     }
   } else {
-    if (m->owns_root()) {
-      LIFEB200_CUDA(cudaSetDevice(c0->device));
-      if (int rc = ensure_scratch(m->d_gather, m->gather_cap, total * sizeof(lifeb200_hit))) return rc;
-    }
-    char* root_buf = static_cast<char*>(m->d_gather);
-    stamp("gather buffer ready");
+    // rank 0's own list already sits at the front of its hit buffer, which the call sized for the whole list before
+    // the shards ran (no allocation here: growing a buffer after NCCL has mapped the peers cost 48 ms on the box)
+    char* root_buf = m->owns_root() ? static_cast<char*>(c0->d_hitbuf) : nullptr;
+    if (m->owns_root() && c0->hitbuf_cap < total * sizeof(lifeb200_hit))
+      return set_error(LIFEB200_E_ARG, "internal: gather buffer smaller than the hit list");
     LIFEB200_NCCL(g_nccl.GroupStart());
     for (int i = 0; i < k; i++) {
       const int r = m->first_rank + i;
@@ -208,8 +205,6 @@ static int gather_body(lifeb200_multi* m, lifeb200_hit* hits, size_t cap, uint64
     stamp("send / recv enqueued");
     if (m->owns_root()) {
       LIFEB200_CUDA(cudaSetDevice(c0->device));
-      if (cnt[0])
-        LIFEB200_CUDA(cudaMemcpyAsync(root_buf, c0->d_hitbuf, cnt[0] * sizeof(lifeb200_hit), cudaMemcpyDeviceToDevice, c0->stream));
       LIFEB200_CUDA(cudaMemcpyAsync(hits, root_buf, total * sizeof(lifeb200_hit), cudaMemcpyDeviceToHost, c0->stream));
     }
   }
@@ -234,6 +229,32 @@ static int gather(lifeb200_multi* m, lifeb200_hit* hits, size_t cap, uint64_t* c
   return LIFEB200_OK;
 }
 
+// NCCL sets a peer connection up at the first send / recv that uses it (40 ms in one process, 0.4 s across
+// processes on the box): do that once at creation with an 8-byte message per rank, not inside the first batch.
+static int warm_connections(lifeb200_multi* m) {
+  const int world = m->world, k = m->n_local();
+  LIFEB200_NCCL(g_nccl.GroupStart());
+  for (int i = 0; i < k; i++)
+    LIFEB200_NCCL(g_nccl.AllGather(m->ctx[i]->d_counters, m->d_allc[i], 4, ncclUint64, m->comm[i], m->ctx[i]->stream));
+  LIFEB200_NCCL(g_nccl.GroupEnd());
+  LIFEB200_NCCL(g_nccl.GroupStart());
+  for (int i = 0; i < k; i++) {
+    const int r = m->first_rank + i;
+    if (r == 0) {
+      for (int src = 1; src < world; src++)
+        LIFEB200_NCCL(g_nccl.Recv(static_cast<char*>(m->d_allc[i]) + 8 * src, 8, ncclUint8, src, m->comm[i], m->ctx[i]->stream));
+    } else {
+      LIFEB200_NCCL(g_nccl.Send(m->ctx[i]->d_counters, 8, ncclUint8, 0, m->comm[i], m->ctx[i]->stream));
+    }
+  }
+  LIFEB200_NCCL(g_nccl.GroupEnd());
+  for (int i = 0; i < k; i++) {
+    LIFEB200_CUDA(cudaSetDevice(m->ctx[i]->device));
+    LIFEB200_CUDA(cudaStreamSynchronize(m->ctx[i]->stream));
+  }
+  return LIFEB200_OK;
+}
+
 static int finish_create(lifeb200_multi* m) {
   LIFEB200_CUDA(cudaSetDevice(m->ctx[0]->device));
   LIFEB200_CUDA(cudaEventCreate(&m->ev0));
@@ -245,6 +266,11 @@ static int finish_create(lifeb200_multi* m) {
       LIFEB200_CUDA(cudaMalloc(&m->d_allc[i], (size_t)m->world * 4 * 8));
     }
     LIFEB200_CUDA(cudaMallocHost(&m->h_allc, (size_t)m->world * 4 * 8));
+    for (int i = 0; i < m->n_local(); i++) {
+      LIFEB200_CUDA(cudaSetDevice(m->ctx[i]->device));
+      LIFEB200_CUDA(cudaMemsetAsync(m->ctx[i]->d_counters, 0, 8 * sizeof(unsigned long long), m->ctx[i]->stream));
+    }
+    return warm_connections(m);
   }
   return LIFEB200_OK;
 }
@@ -267,7 +293,6 @@ int lifeb200_multi_destroy(lifeb200_multi* m) {
     if (m->ev0) cudaEventDestroy(m->ev0);
     if (m->ev1) cudaEventDestroy(m->ev1);
   }
-  if (m->d_gather && !m->ctx.empty()) { cudaSetDevice(m->ctx[0]->device); cudaFree(m->d_gather); }
   for (lifeb200_ctx* c : m->ctx) lifeb200_destroy(c);
   delete m;
   return LIFEB200_OK;
@@ -403,10 +428,12 @@ int lifeb200_multi_soup_survey(lifeb200_multi* m, uint64_t first_id, uint64_t n,
     shard(first_id, n, m->first_rank + i, m->world, &b, &e);
     std::memset(c->h_counters, 0, 4 * sizeof(unsigned long long));
     LIFEB200_CUDA(cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream));
-    if (e == b) { LIFEB200_CUDA(cudaStreamSynchronize(c->stream)); return LIFEB200_OK; }
     // a shard can report at most its own ids and never more than the caller can take
     const size_t shard_cap = (size_t)std::min<uint64_t>(e - b, cap);
-    if (int r = ensure_scratch(c->d_hitbuf, c->hitbuf_cap, std::max<size_t>(shard_cap, 1) * sizeof(lifeb200_hit))) return r;
+    // rank 0's buffer doubles as the gather buffer: room for the whole list the caller can take
+    const size_t room = (m->first_rank + i == 0) ? (size_t)std::min<uint64_t>(n, cap) : shard_cap;
+    if (int r = ensure_scratch(c->d_hitbuf, c->hitbuf_cap, std::max<size_t>(room, 1) * sizeof(lifeb200_hit))) return r;
+    if (e == b) { LIFEB200_CUDA(cudaStreamSynchronize(c->stream)); return LIFEB200_OK; }
     return survey_to_device(c, b, (size_t)(e - b), seed, dist, gens, static_cast<lifeb200_hit*>(c->d_hitbuf), shard_cap);
   });
   if (rc) return rc;
@@ -439,9 +466,10 @@ int lifeb200_multi_enumerate_collisions(lifeb200_multi* m, const uint64_t* catal
     shard(id_begin, id_end - id_begin, m->first_rank + i, m->world, &b, &e);
     std::memset(c->h_counters, 0, 4 * sizeof(unsigned long long));
     LIFEB200_CUDA(cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream));
-    if (e == b) { LIFEB200_CUDA(cudaStreamSynchronize(c->stream)); return LIFEB200_OK; }
     const size_t shard_cap = (size_t)std::min<uint64_t>(e - b, cap);
-    if (int r = ensure_scratch(c->d_hitbuf, c->hitbuf_cap, std::max<size_t>(shard_cap, 1) * sizeof(lifeb200_hit))) return r;
+    const size_t room = (m->first_rank + i == 0) ? (size_t)std::min<uint64_t>(id_end - id_begin, cap) : shard_cap;
+    if (int r = ensure_scratch(c->d_hitbuf, c->hitbuf_cap, std::max<size_t>(room, 1) * sizeof(lifeb200_hit))) return r;
+    if (e == b) { LIFEB200_CUDA(cudaStreamSynchronize(c->stream)); return LIFEB200_OK; }
     return enumerate_to_device(c, catalysts, n_catalysts, projectiles, n_projectiles, b, e, gens, stable_interval,
                                static_cast<lifeb200_hit*>(c->d_hitbuf), shard_cap);
   });

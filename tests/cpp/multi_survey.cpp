@@ -4,6 +4,7 @@
 // plain context API and checks that the two lists are byte-identical (BASELINE config 5 with defaults on 8 GPUs:
 //   multi_survey 16777216 4096).
 // Build: g++ -std=c++17 -O2 -Iinclude tests/cpp/multi_survey.cpp -o multi_survey lifeapi_b200/_lib/liblifeapi_b200.so
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -29,7 +30,7 @@ int main(int argc, char** argv) {
   LifeMultiBatch group(want_gpus);  // lifeb200_multi_create over the first want_gpus devices (0: every visible one)
   std::vector<LifeHit> hits(n / 8 + 4096);  // room for one hit in eight ids: a list that does not fit costs a second full run
   uint64_t pop_sum = 0, hash_xor = 0;
-  group.SoupSurvey(0, 4096 * (uint64_t)group.World(), seed, 0, 16, hits, &pop_sum, &hash_xor);  // warm-up: NCCL channels, scratch
+  group.SoupSurvey(0, std::min<uint64_t>(n, hits.size()), seed, 0, 2, hits, &pop_sum, &hash_xor);  // warm-up: kernel image, buffers at final size
   const auto t0 = std::chrono::steady_clock::now();
   const size_t nh = group.SoupSurvey(0, n, seed, 0, gens, hits, &pop_sum, &hash_xor);
   const double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
