@@ -1,4 +1,9 @@
-"""Batch sharding and the hit-list gather.
+"""Batch sharding and a torch.distributed hit-list gather -- the PYTHON-side helper.
+
+Since round 2 the product's multi-GPU path is inside the C library (csrc/multi.cu: lifeb200_multi_*, NCCL gather of
+device-resident sorted hit lists; capi.MultiEngine) and bench.py uses that.  What stays here is what a Python caller
+with its own process group may still want: the shard split, the optional NUMA binding, and a gather of host-side hit
+arrays over whatever backend the group has (gloo in the CPU tests).
 
 Patterns are independent and the 64x64 torus is closed, so the stepping path needs no exchange:
 rank r of R owns the contiguous id range [r*n/R, (r+1)*n/R).  The only collective is one small
