@@ -401,6 +401,12 @@ struct LifeWeld {
     lifeb200::Check(lifeb200_weld_step_batch_host(lifeb200::DefaultContext(), state.state, 1, numIters), "LifeWeld::Step");
   }
   LifeTarget ToTarget() const;  // LifeWeld.hpp:188-191 (defined after LifeTarget)
+  LifeState InteractionOffsets(const LifeWeld& b) const {  // LifeWeld.hpp:217-262
+    LifeState r;
+    lifeb200::Check(lifeb200_weld_interaction_offsets_host(lifeb200::DefaultContext(), state.state, 1, b.state.state, 1, r.state, 1),
+                    "LifeWeld::InteractionOffsets");
+    return r;
+  }
   void InteractionCounts(LifeState& out1, LifeState& out2, LifeState& outMore) const {  // LifeWeld.hpp:193-215
     alignas(64) uint64_t planes[3 * N];
     lifeb200::Check(lifeb200_weld_interaction_counts_host(lifeb200::DefaultContext(), state.state, planes, 1), "LifeWeld::InteractionCounts");

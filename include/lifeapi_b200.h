@@ -290,6 +290,13 @@ int lifeb200_interaction_offsets_dev(lifeb200_ctx* ctx, const uint64_t* a, size_
 int lifeb200_interaction_offsets_host(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
                                       uint64_t* out, size_t n);
 
+/* LifeWeld::InteractionOffsets (LifeWeld.hpp:217-262): the same for two LifeWeld records (state, frozen2, frozen1,
+ * frozen0 = 2048 B each), interactions that involve frozen cells left out. */
+int lifeb200_weld_interaction_offsets_dev(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                          uint64_t* out, size_t n);
+int lifeb200_weld_interaction_offsets_host(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                           uint64_t* out, size_t n);
+
 /* ---- 8f rank 4: RLE in and out (host functions; strings are a host format) ---------------
  * LifeState::RLE (Parsing.hpp:8-66,198-202) / LifeHistory::RLE (LifeHistory.hpp:25-44,62-68): writes
  * the NUL-terminated string into buf (capacity cap) and its length into *len; LIFEB200_E_OVERFLOW

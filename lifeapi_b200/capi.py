@@ -134,6 +134,8 @@ SIGNATURES = {
     "lifeb200_match_target_batch_host": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp]),
     "lifeb200_interaction_offsets_dev": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t]),
     "lifeb200_interaction_offsets_host": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t]),
+    "lifeb200_weld_interaction_offsets_dev": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t]),
+    "lifeb200_weld_interaction_offsets_host": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t]),
     "lifeb200_rle": (C.c_int, [_vp, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
     "lifeb200_history_rle": (C.c_int, [_vp, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
     "lifeb200_parse_rle": (C.c_int, [C.c_char_p, _vp]),
@@ -649,6 +651,14 @@ class Engine:
         (states, n), (targets, nt) = self._planes(states), self._planes(targets, 2 * WORDS)
         out = np.empty((n, WORDS), dtype=np.uint64)
         self._check(self.lib.lifeb200_match_target_batch_host(self._h, _ptr(states), n, _ptr(targets), nt, _ptr(out)))
+        return out
+
+    def weld_interaction_offsets_host(self, a: np.ndarray, b: np.ndarray) -> np.ndarray:
+        """a, b: (n or 1, 4, 64) LifeWeld records -> (n, 64) offsets plane."""
+        (a, na), (b, nb) = self._planes(a, 4 * WORDS), self._planes(b, 4 * WORDS)
+        n = max(na, nb)
+        out = np.empty((n, WORDS), dtype=np.uint64)
+        self._check(self.lib.lifeb200_weld_interaction_offsets_host(self._h, _ptr(a), na, _ptr(b), nb, _ptr(out), n))
         return out
 
     def interaction_offsets_dev(self, d_a, n_a: int, d_b, n_b: int, d_out, n: int) -> None:

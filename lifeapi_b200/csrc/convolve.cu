@@ -195,6 +195,42 @@ __global__ void __launch_bounds__(kBlockC) interaction_offsets_kernel(const uint
   store_plane(out + p * kN, lane, r);
 }
 
+// LifeWeld::InteractionOffsets (LifeWeld.hpp:217-262): InteractionOffsets of the two states with the interactions that
+// involve frozen cells left out -- every operand is masked by the zone of influence of its weld's NON-frozen cells.
+// The expressions follow the reference member term by term, including which `ignored` mask each operand carries
+// (its second and third terms mask the OTHER weld's operand with the first weld's zone: kept, parity is bit-exact).
+// Records are LifeWeld layouts: state, frozen2, frozen1, frozen0 (4 x 64 words).
+__global__ void __launch_bounds__(kBlockC) weld_interaction_offsets_kernel(const uint64_t* __restrict__ a, size_t n_a,
+                                                                           const uint64_t* __restrict__ b, size_t n_b,
+                                                                           uint64_t* __restrict__ out, size_t n) {
+  const size_t p = ((size_t)blockIdx.x * kBlockC + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (p >= n) return;
+  const uint64_t* ra = a + (n_a == 1 ? 0 : p) * 4 * kN;
+  const uint64_t* rb = b + (n_b == 1 ? 0 : p) * 4 * kN;
+  const Plane A = load_plane(ra, lane);
+  const Plane a_free = A & ~load_plane(ra + kN, lane) & ~load_plane(ra + 2 * kN, lane) & ~load_plane(ra + 3 * kN, lane);
+  const Plane a_zone = to_plane(dilate<32>(to_tile(a_free), lane, false));  // ~a_ignored
+  const Plane Bs = load_plane(rb, lane);
+  const Plane b_free = Bs & ~load_plane(rb + kN, lane) & ~load_plane(rb + 2 * kN, lane) & ~load_plane(rb + 3 * kN, lane);
+  const Plane B = mirrored(Bs, lane);
+  const Plane b_zone = mirrored(to_plane(dilate<32>(to_tile(b_free), lane, false)), lane);  // ~b_ignored
+  Tile<32> t3, t2, t1, t0;
+  to_tile(A).neighbour_count(lane, t3, t2, t1, t0);
+  const Plane a3 = to_plane(t3), a2 = to_plane(t2), a1 = to_plane(t1), a0 = to_plane(t0);
+  to_tile(B).neighbour_count(lane, t3, t2, t1, t0);
+  const Plane b3 = to_plane(t3), b2 = to_plane(t2), b1 = to_plane(t1), b0 = to_plane(t0);
+  const Plane a_lo = ~a3 & ~a2, b_lo = ~b3 & ~b2;
+  Plane r = convolve(A, B, lane);                                                                        // overlaps
+  r = r | convolve(a_lo & ~a1 & a0 & ~A & a_zone, b_lo & b1 & ~b0 & ~B & a_zone, lane);                  // births
+  r = r | convolve(b_lo & ~b1 & b0 & ~B & b_zone, a_lo & a1 & ~a0 & ~A & b_zone, lane);
+  r = r | convolve(a_lo & a1 & a0 & A & a_zone, (b3 | b2 | b1) & ~B & b_zone, lane);                      // overcrowding
+  r = r | convolve((a2 | a3) & A & a_zone, (b3 | b2 | b1 | b0) & ~B & b_zone, lane);
+  r = r | convolve(b_lo & b1 & b0 & B & b_zone, (a3 | a2 | a1) & ~A & a_zone, lane);
+  r = r | convolve((b2 | b3) & B & b_zone, (a3 | a2 | a1 | a0) & ~A & a_zone, lane);
+  store_plane(out + p * kN, lane, r);
+}
+
 // ---- host-pointer variants: up to three plane inputs, each either per-problem or broadcast ----
 struct HostIn {
   const uint64_t* ptr;
@@ -424,6 +460,27 @@ int lifeb200_contains_target_batch_host(lifeb200_ctx* ctx, const uint64_t* state
   const int rc = body();
   if (rc) drain_slots(ctx, used);
   return rc;
+}
+
+int lifeb200_weld_interaction_offsets_dev(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                          uint64_t* out, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (int rc = check_pair(a, n_a, b, n_b, out, n, true)) return rc;
+  weld_interaction_offsets_kernel<<<grid_warps(n), kBlockC, 0, ctx->stream>>>(a, n_a, b, n_b, out, n);
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
+}
+
+int lifeb200_weld_interaction_offsets_host(lifeb200_ctx* ctx, const uint64_t* a, size_t n_a, const uint64_t* b, size_t n_b,
+                                           uint64_t* out, size_t n) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (n == 0) return LIFEB200_OK;
+  if (int rc = check_pair(a, n_a, b, n_b, out, n, false)) return rc;
+  const HostIn ins[2] = {{a, n_a, (size_t)(4 * kN)}, {b, n_b, (size_t)(4 * kN)}};
+  return planes_host(ctx, ins, 2, out, n, [&](const uint64_t* const* d, uint64_t* dout, size_t cnt, cudaStream_t st) {
+    weld_interaction_offsets_kernel<<<grid_warps(cnt), kBlockC, 0, st>>>(d[0], n_a == 1 ? 1 : cnt, d[1], n_b == 1 ? 1 : cnt, dout, cnt);
+  });
 }
 
 }  // extern "C"

@@ -387,6 +387,7 @@ class Ref:
         _sig(lib, "ref_weld_step_batch", None, [_u64p, C.c_size_t, C.c_uint, C.c_int])
         _sig(lib, "ref_interaction_counts_batch", None, [_u64p, C.c_size_t, _u64p, C.c_int])
         _sig(lib, "ref_weld_interaction_counts_batch", None, [_u64p, C.c_size_t, _u64p, C.c_int])
+        _sig(lib, "ref_weld_interaction_offsets_batch", None, [_u64p, C.c_size_t, _u64p, C.c_size_t, C.c_size_t, _u64p, C.c_int])
         _sig(lib, "ref_nc_add_batch", None, [_u64p, _u64p, C.c_void_p, C.c_size_t, _u64p, C.c_int])
         _sig(lib, "ref_nc_subtract_batch", None, [_u64p, _u64p, C.c_size_t, _u64p, C.c_int])
         _sig(lib, "ref_nc_with_exactly_batch", None, [_u64p, C.c_size_t, C.c_uint, _u64p, C.c_int])
@@ -447,6 +448,14 @@ class Ref:
         r = aligned_copy(np.asarray(records, dtype=np.uint64).reshape(-1, 4, 64))
         out = aligned_copy(np.zeros((r.shape[0], 3, 64), dtype=np.uint64))
         self.lib.ref_weld_interaction_counts_batch(r.reshape(-1), r.shape[0], out.reshape(-1), threads)
+        return out
+
+    def weld_interaction_offsets_batch(self, a, b, threads: int = 0) -> np.ndarray:
+        a = aligned_copy(np.asarray(a, dtype=np.uint64).reshape(-1, 4, 64))
+        b = aligned_copy(np.asarray(b, dtype=np.uint64).reshape(-1, 4, 64))
+        n = max(a.shape[0], b.shape[0])
+        out = aligned_copy(np.zeros((n, 64), dtype=np.uint64))
+        self.lib.ref_weld_interaction_offsets_batch(a.reshape(-1), a.shape[0], b.reshape(-1), b.shape[0], n, out.reshape(-1), threads)
         return out
 
     def nc_add_batch(self, a, b, incarry=None, threads: int = 0) -> np.ndarray:

@@ -90,6 +90,19 @@ void ref_weld_interaction_counts_batch(const uint64_t *recs, size_t n, uint64_t 
   });
 }
 
+// LifeWeld::InteractionOffsets (LifeWeld.hpp:217-262): out[i] = a[i or 0].InteractionOffsets(b[i or 0]).
+void ref_weld_interaction_offsets_batch(const uint64_t *a, size_t n_a, const uint64_t *b, size_t n_b, size_t n, uint64_t *out,
+                                        int threads) {
+  parallel_chunks(n, threads, [=](size_t lo, size_t hi, int) {
+    for (size_t i = lo; i < hi; i++) {
+      LifeWeld x, y;
+      std::memcpy(static_cast<void *>(&x), a + 256 * (n_a == 1 ? 0 : i), sizeof x);
+      std::memcpy(static_cast<void *>(&y), b + 256 * (n_b == 1 ? 0 : i), sizeof y);
+      store(x.InteractionOffsets(y), out + 64 * i);
+    }
+  });
+}
+
 // NeighbourCount arithmetic over batches of 2048-byte records (NeighbourCount.hpp:71-102).
 void ref_nc_add_batch(const uint64_t *a, const uint64_t *b, const uint64_t *incarry, size_t n, uint64_t *out, int threads) {
   parallel_chunks(n, threads, [=](size_t lo, size_t hi, int) {

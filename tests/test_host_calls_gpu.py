@@ -154,3 +154,30 @@ def test_weld_interaction_counts_vs_reference(engine, ref, port):
     plain[:, 1:] = 0  # no frozen cells: LifeState::InteractionCounts masked by the state's own ZOI (a no-op on these planes)
     got = engine.weld_interaction_counts_host(plain)
     assert (got == engine.interaction_counts_host(plain[:, 0])[:, :3]).all()
+
+
+def test_weld_interaction_offsets_vs_reference(engine, ref, port):
+    """LifeWeld::InteractionOffsets (LifeWeld.hpp:217-262): one welded catalyst against many small objects (shared
+    operand), per-problem pairs, and welds without frozen cells."""
+    n = 300
+    eater = port.parse("2b2o$bobo$bo$2o!", 20, 20)
+    cat = np.zeros((1, 4, 64), dtype=np.uint64)
+    cat[0, 0] = eater
+    cat[0, 3] = port.parse("2o!", 22, 23)           # two stator cells frozen ...
+    cat[0, 2] = port.parse("o!", 19, 22)            # ... and a frozen count on a dead neighbour
+    box = np.zeros(64, dtype=np.uint64)
+    box[:8] = np.uint64(0xFF)
+    objs = np.zeros((n, 4, 64), dtype=np.uint64)
+    objs[:, 0] = port.soup(4000, n, SEED, 0) & port.soup(8000, n, SEED, 0) & box
+    objs[::2, 3] = objs[::2, 0] & port.soup(12000, n, SEED, 0)[::2]   # half of the objects have frozen cells too
+    got = engine.weld_interaction_offsets_host(cat, objs)
+    assert (got == ref.weld_interaction_offsets_batch(cat, objs, 0)).all()
+    got2 = engine.weld_interaction_offsets_host(objs, np.roll(objs, 1, axis=0))
+    assert (got2 == ref.weld_interaction_offsets_batch(objs, np.roll(objs, 1, axis=0), 0)).all()
+    # no frozen cells anywhere: still the reference's member (its second and third terms mask the OTHER weld's operand
+    # with the first weld's zone, so this is NOT LifeState::InteractionOffsets -- the quirk is part of the parity)
+    plain = objs.copy()
+    plain[:, 1:] = 0
+    pc = cat.copy()
+    pc[:, 1:] = 0
+    assert (engine.weld_interaction_offsets_host(pc, plain) == ref.weld_interaction_offsets_batch(pc, plain, 0)).all()
