@@ -2,6 +2,8 @@
 // placement construction (Moved/operator|, LifeAPI.hpp:699-717,247-253), the soup survey with the
 // period-2 activity test (operator==, LifeAPI.hpp:213-220) and hit compaction.
 #include <algorithm>
+#include <chrono>
+#include <cstdlib>
 #include <vector>
 
 #include "ctx.h"
@@ -747,7 +749,15 @@ int enumerate_to_device(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n
 
 int survey_to_device(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t seed, int dist, unsigned gens,
                      lifeb200_hit* d_hits, size_t cap) {
+  static const bool trace = std::getenv("LIFEB200_TRACE_GATHER") != nullptr;
+  const auto t0 = std::chrono::steady_clock::now();
+  auto stamp = [&](const char* what) {
+    if (trace)
+      std::fprintf(stderr, "[lifeb200 survey dev %d] %-20s +%.3f ms\n", ctx->device, what,
+                   std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+  };
   if (int rc = ensure_dense(ctx, n)) return rc;
+  stamp("scratch ready");
   uint64_t* dense = static_cast<uint64_t*>(ctx->d_dense);
   LIFEB200_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
   // many generations: 4 soups per lane group in the row-class layout (life_multi.cuh), unless the caller
@@ -763,10 +773,13 @@ int survey_to_device(lifeb200_ctx* ctx, uint64_t first_id, size_t n, uint64_t se
                                         first_id, n, seed, dist, gens, dense, ctx->d_counters + 2, ctx->d_counters + 3)));
   }
   LIFEB200_LAUNCHED(ctx);
+  stamp("kernel launched");
   if (int rc = compact_hits(ctx, n, first_id, d_hits, cap, ctx->d_counters + 0)) return rc;
   LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
                                 ctx->stream));
+  stamp("all enqueued");
   LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
+  stamp("stream drained");
   return LIFEB200_OK;
 }
 

@@ -115,16 +115,26 @@ template <class F>
 static int for_each_device(lifeb200_multi* m, F fn) {
   const int k = m->n_local();
   if (k == 1) return fn(0);
+  static const bool trace = std::getenv("LIFEB200_TRACE_GATHER") != nullptr;
+  const auto t0 = std::chrono::steady_clock::now();
+  auto ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
   std::vector<int> rc(k, LIFEB200_OK);
   std::vector<std::string> msg(k);
+  std::vector<double> t_in(k), t_out(k);
   std::vector<std::thread> pool;
   pool.reserve(k);
   for (int i = 0; i < k; i++)
     pool.emplace_back([&, i] {
+      t_in[i] = ms();
       rc[i] = fn(i);
+      t_out[i] = ms();
       if (rc[i]) msg[i] = lifeb200_last_error();  // the error text is per thread: carry it to the caller's
     });
   for (auto& t : pool) t.join();
+  if (trace)
+    for (int i = 0; i < k; i++)
+      std::fprintf(stderr, "[lifeb200 shard rank %d] thread in +%.3f ms, out +%.3f ms (joined +%.3f ms)\n", m->first_rank + i, t_in[i],
+                   t_out[i], ms());
   for (int i = 0; i < k; i++)
     if (rc[i]) return set_error(rc[i], "device %d (rank %d): %s", m->ctx[i]->device, m->first_rank + i, msg[i].c_str());
   return LIFEB200_OK;
