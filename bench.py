@@ -372,7 +372,8 @@ def main():
         try:
             cap5 = total5
             h_hits = np.zeros(cap5 if rank == 0 else 1, dtype=HIT_DTYPE)
-            group.soup_survey(0, total5, SEED, 0, 2, cap5, hits=h_hits)  # untimed: kernel image, scratch and gather buffers at their final size
+            group.reserve(total5, cap5)  # scratch and gather buffers at their final size: no allocation in the timed call
+            group.soup_survey(0, min(total5, world << 14), SEED, 0, 16, cap5, hits=h_hits)  # untimed: kernel image
             barrier()
             t0 = time.perf_counter()
             merged, ps5, hx5 = group.soup_survey(0, total5, SEED, 0, gens5, cap5, hits=h_hits)

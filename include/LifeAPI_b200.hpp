@@ -576,6 +576,8 @@ class LifeMultiBatch {
 
   int World() const { int w = 0; lifeb200_multi_info(m_, &w, nullptr, nullptr, nullptr); return w; }
   int NcclVersion() const { int v = 0; lifeb200_multi_info(m_, nullptr, nullptr, nullptr, &v); return v; }
+  // size the scratch of every GPU for calls over up to n ids / cap hit records (no allocation in later calls of that size)
+  void Reserve(uint64_t n, size_t cap) { lifeb200::Check(lifeb200_multi_reserve(m_, n, cap), "lifeb200_multi_reserve"); }
   float LastGatherMs() const { float ms = 0; lifeb200_multi_last_gather_ms(m_, &ms); return ms; }
   lifeb200_ctx* Context(int local_index) const { lifeb200_ctx* c = nullptr; lifeb200::Check(lifeb200_multi_ctx(m_, local_index, &c), "lifeb200_multi_ctx"); return c; }
 

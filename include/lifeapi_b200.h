@@ -336,6 +336,10 @@ int lifeb200_multi_shard(lifeb200_multi* m, uint64_t first_id, uint64_t n, int r
 int lifeb200_multi_set_gather(lifeb200_multi* m, int mode);
 /* Device time of the last call's gather (counters + hit lists + download), CUDA events on local GPU 0. */
 int lifeb200_multi_last_gather_ms(lifeb200_multi* m, float* ms);
+/* Size every local GPU's scratch (dense results, hit records, rank 0's gather room) for calls over up to `n` ids with
+ * hit capacity `cap`, so that no later call of that size allocates: growing a device buffer once NCCL has mapped the
+ * peers costs milliseconds per GPU and serialises across the GPUs of a process.  Optional: calls grow on demand. */
+int lifeb200_multi_reserve(lifeb200_multi* m, uint64_t n, size_t cap);
 /* lifeb200_soup_survey / lifeb200_enumerate_collisions over the whole group (same arguments, HOST hit buffer). */
 int lifeb200_multi_soup_survey(lifeb200_multi* m, uint64_t first_id, uint64_t n, uint64_t seed, int dist, unsigned gens,
                                lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* pop_sum, uint64_t* hash_xor);

@@ -109,6 +109,7 @@ SIGNATURES = {
     "lifeb200_multi_shard": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_int, _u64p, _u64p]),
     "lifeb200_multi_set_gather": (C.c_int, [_vp, C.c_int]),
     "lifeb200_multi_last_gather_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "lifeb200_multi_reserve": (C.c_int, [_vp, C.c_uint64, C.c_size_t]),
     "lifeb200_multi_soup_survey": (C.c_int, [_vp, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.c_uint, _vp, C.c_size_t,
                                              _u64p, _u64p, _u64p]),
     "lifeb200_multi_enumerate_collisions": (C.c_int, [_vp, _vp, C.c_uint, _vp, C.c_uint, C.c_uint64, C.c_uint64, C.c_uint,
@@ -748,6 +749,9 @@ class MultiEngine:
         b, e = C.c_uint64(), C.c_uint64()
         self._check(self.lib.lifeb200_multi_shard(self._h, first_id, n, rank, C.byref(b), C.byref(e)))
         return b.value, e.value
+
+    def reserve(self, n: int, cap: int) -> None:
+        self._check(self.lib.lifeb200_multi_reserve(self._h, n, cap))
 
     def set_gather(self, mode: int) -> None:
         self._check(self.lib.lifeb200_multi_set_gather(self._h, mode))

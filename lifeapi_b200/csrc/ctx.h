@@ -71,6 +71,8 @@ int enumerate_to_device(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n
                         unsigned n_projectiles, uint64_t id_begin, uint64_t id_end, unsigned gens, unsigned stable_interval,
                         lifeb200_hit* d_hits, size_t cap);
 
+int reserve_ids(lifeb200_ctx* ctx, size_t n);  // size the dense-result / tile scratch for calls over n ids
+
 #define LIFEB200_CUDA(expr)                                                        \
   do {                                                                             \
     cudaError_t _e = (expr);                                                       \

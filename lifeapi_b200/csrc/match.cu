@@ -642,6 +642,8 @@ static int ensure_dense(lifeb200_ctx* ctx, size_t n) {
   return ensure_scratch(ctx->d_tiles, ctx->tiles_cap, tiles * sizeof(unsigned long long));
 }
 
+int reserve_ids(lifeb200_ctx* ctx, size_t n) { return ensure_dense(ctx, n); }
+
 // dense[0..n) -> hits[0..min(found, cap)) in id order, found -> *d_n_hits (device); three launches on the stream
 static int compact_hits(lifeb200_ctx* ctx, size_t n, uint64_t first_id, lifeb200_hit* d_hits, size_t cap,
                         unsigned long long* d_n_hits) {

@@ -422,6 +422,20 @@ int lifeb200_multi_shard(lifeb200_multi* m, uint64_t first_id, uint64_t n, int r
   return LIFEB200_OK;
 }
 
+int lifeb200_multi_reserve(lifeb200_multi* m, uint64_t n, size_t cap) {
+  if (!m) return set_error(LIFEB200_E_ARG, "null group");
+  return for_each_device(m, [&](int i) -> int {
+    lifeb200_ctx* c = m->ctx[i];
+    LIFEB200_CUDA(cudaSetDevice(c->device));
+    uint64_t b, e;
+    shard(0, n, m->first_rank + i, m->world, &b, &e);
+    const size_t shard_cap = (size_t)std::min<uint64_t>(e - b, cap);
+    const size_t room = (m->first_rank + i == 0) ? (size_t)std::min<uint64_t>(n, cap) : shard_cap;
+    if (int r = ensure_scratch(c->d_hitbuf, c->hitbuf_cap, std::max<size_t>(room, 1) * sizeof(lifeb200_hit))) return r;
+    return reserve_ids(c, (size_t)std::max<uint64_t>(e - b, 1));
+  });
+}
+
 int lifeb200_multi_soup_survey(lifeb200_multi* m, uint64_t first_id, uint64_t n, uint64_t seed, int dist, unsigned gens,
                                lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* pop_sum, uint64_t* hash_xor) {
   if (!m) return set_error(LIFEB200_E_ARG, "null group");

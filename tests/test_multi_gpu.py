@@ -108,6 +108,7 @@ def test_multi_group_info(groups):
 
 def test_multi_survey_equals_single_engine(groups, engine, port):
     for g in groups:
+        g.reserve(4099, 4099)
         for mode in ((0, 1) if g.info()["world"] > 1 else (0,)):
             g.set_gather(mode)
             for (first, n, dist, gens) in [(0, 4099, 0, 96), (1 << 33, 1000, 1, 130), (3, 5, 0, 20), (9, 0, 0, 4)]:
