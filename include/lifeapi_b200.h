@@ -41,7 +41,8 @@ enum {
   LIFEB200_E_ARG = 2,       /* bad argument (null / misaligned pointer, bad enum) */
   LIFEB200_E_OVERFLOW = 3,  /* hit buffer too small: *n_hits holds the required count */
   LIFEB200_E_NODEVICE = 4,  /* no CUDA device / wrong architecture */
-  LIFEB200_E_NCCL = 5       /* NCCL could not be loaded or a collective failed (multi-GPU groups only) */
+  LIFEB200_E_NCCL = 5,      /* NCCL could not be loaded or a collective failed (multi-GPU groups only) */
+  LIFEB200_E_HOST = 6       /* host-side failure inside the library (out of host memory, thread creation) */
 };
 
 typedef struct lifeb200_ctx lifeb200_ctx; /* opaque: device, stream, scratch, pinned staging */

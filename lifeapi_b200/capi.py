@@ -20,7 +20,7 @@ HEADER_PATH = os.path.join(HERE, "..", "include", "lifeapi_b200.h")
 WORDS = 64
 PATTERN_BYTES = 512
 
-E_OK, E_CUDA, E_ARG, E_OVERFLOW, E_NODEVICE, E_NCCL = 0, 1, 2, 3, 4, 5
+E_OK, E_CUDA, E_ARG, E_OVERFLOW, E_NODEVICE, E_NCCL, E_HOST = 0, 1, 2, 3, 4, 5, 6
 UNIQUE_ID_BYTES = 128
 
 STABLE_WORDS = 640

@@ -1,5 +1,6 @@
 // ctx.cu -- context, memory, error and timing entry points of the C ABI (include/lifeapi_b200.h).
 #include <cstring>
+#include <new>
 
 #include "ctx.h"
 
@@ -84,7 +85,8 @@ int lifeb200_create(int device, lifeb200_ctx** out) {
   if (prop.major != 10)
     return set_error(LIFEB200_E_NODEVICE, "device %d is sm_%d%d; kernels are built for sm_100a only", device, prop.major,
                      prop.minor);
-  lifeb200_ctx* c = new lifeb200_ctx();
+  lifeb200_ctx* c = new (std::nothrow) lifeb200_ctx();
+  if (!c) return set_error(LIFEB200_E_HOST, "out of host memory");
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
   c->cc_major = prop.major;

@@ -3,6 +3,8 @@
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <exception>
+#include <new>
 #include <cuda_runtime.h>
 
 #include "../../include/lifeapi_b200.h"
@@ -119,5 +121,20 @@ inline int effective_lpp(const lifeb200_ctx* ctx) { return ctx->lpp ? ctx->lpp :
     case 32: { constexpr int LPP = 32; CALL; } break; \
     default: return lifeb200::set_error(LIFEB200_E_ARG, "lanes per pattern must be 4,8,16,32 for this kernel"); \
   }
+
+// No C++ exception may cross the extern "C" boundary: entry points that allocate host memory or start threads run
+// their body through this (std::bad_alloc, std::system_error from std::thread, ...) and report LIFEB200_E_HOST.
+template <class F>
+inline int guarded(F body) {
+  try {
+    return body();
+  } catch (const std::bad_alloc&) {
+    return set_error(LIFEB200_E_HOST, "out of host memory");
+  } catch (const std::exception& e) {
+    return set_error(LIFEB200_E_HOST, "host-side failure: %s", e.what());
+  } catch (...) {
+    return set_error(LIFEB200_E_HOST, "host-side failure");
+  }
+}
 
 }  // namespace lifeb200

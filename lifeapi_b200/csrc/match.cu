@@ -672,8 +672,14 @@ static uint64_t table_key(const uint64_t* a, size_t na, const uint64_t* b, size_
 // planes (every cell of wanted = catalyst and of mask = its ZOI replicated into the four pattern bits of register
 // (column, k)).  Built and uploaded once per distinct table content: a sharded caller walks one table set over
 // many id ranges, and the context keeps the last set keyed by a hash of its words.
+static int ensure_tables_body(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts, const uint64_t* projectiles,
+                              unsigned n_projectiles);
 static int ensure_tables(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts, const uint64_t* projectiles,
                          unsigned n_projectiles) {
+  return guarded([&]() -> int { return ensure_tables_body(ctx, catalysts, n_catalysts, projectiles, n_projectiles); });
+}
+static int ensure_tables_body(lifeb200_ctx* ctx, const uint64_t* catalysts, unsigned n_catalysts, const uint64_t* projectiles,
+                              unsigned n_projectiles) {
   const uint64_t key = table_key(catalysts, (size_t)n_catalysts * 64, projectiles, (size_t)n_projectiles * 64);
   if (ctx->tab_valid && ctx->tab_key == key && ctx->tab_ncat == n_catalysts && ctx->tab_nproj == n_projectiles)
     return LIFEB200_OK;

@@ -308,7 +308,7 @@ int lifeb200_multi_destroy(lifeb200_multi* m) {
   return LIFEB200_OK;
 }
 
-int lifeb200_multi_create(const int* devices, int n_devices, lifeb200_multi** out) {
+static int lifeb200_multi_create_body(const int* devices, int n_devices, lifeb200_multi** out) {
   if (!out) return set_error(LIFEB200_E_ARG, "null out");
   *out = nullptr;
   int count = 0;
@@ -354,7 +354,7 @@ int lifeb200_multi_unique_id(char* id128) {
   return LIFEB200_OK;
 }
 
-int lifeb200_multi_create_rank(int device, int rank, int world, const char* id128, lifeb200_multi** out) {
+static int lifeb200_multi_create_rank_body(int device, int rank, int world, const char* id128, lifeb200_multi** out) {
   if (!out) return set_error(LIFEB200_E_ARG, "null out");
   *out = nullptr;
   if (world < 1 || rank < 0 || rank >= world) return set_error(LIFEB200_E_ARG, "bad rank / world %d / %d", rank, world);
@@ -422,7 +422,7 @@ int lifeb200_multi_shard(lifeb200_multi* m, uint64_t first_id, uint64_t n, int r
   return LIFEB200_OK;
 }
 
-int lifeb200_multi_reserve(lifeb200_multi* m, uint64_t n, size_t cap) {
+static int lifeb200_multi_reserve_body(lifeb200_multi* m, uint64_t n, size_t cap) {
   if (!m) return set_error(LIFEB200_E_ARG, "null group");
   return for_each_device(m, [&](int i) -> int {
     lifeb200_ctx* c = m->ctx[i];
@@ -436,7 +436,7 @@ int lifeb200_multi_reserve(lifeb200_multi* m, uint64_t n, size_t cap) {
   });
 }
 
-int lifeb200_multi_soup_survey(lifeb200_multi* m, uint64_t first_id, uint64_t n, uint64_t seed, int dist, unsigned gens,
+static int lifeb200_multi_soup_survey_body(lifeb200_multi* m, uint64_t first_id, uint64_t n, uint64_t seed, int dist, unsigned gens,
                                lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* pop_sum, uint64_t* hash_xor) {
   if (!m) return set_error(LIFEB200_E_ARG, "null group");
   if (gens < 2) return set_error(LIFEB200_E_ARG, "survey needs gens >= 2");
@@ -469,7 +469,7 @@ int lifeb200_multi_soup_survey(lifeb200_multi* m, uint64_t first_id, uint64_t n,
   return rc;
 }
 
-int lifeb200_multi_enumerate_collisions(lifeb200_multi* m, const uint64_t* catalysts, unsigned n_catalysts,
+static int lifeb200_multi_enumerate_collisions_body(lifeb200_multi* m, const uint64_t* catalysts, unsigned n_catalysts,
                                         const uint64_t* projectiles, unsigned n_projectiles, uint64_t id_begin,
                                         uint64_t id_end, unsigned gens, unsigned stable_interval, lifeb200_hit* hits,
                                         size_t cap, uint64_t* n_hits, uint64_t* n_skipped) {
@@ -505,7 +505,7 @@ int lifeb200_multi_enumerate_collisions(lifeb200_multi* m, const uint64_t* catal
   return rc;
 }
 
-int lifeb200_multi_step_batch_host(lifeb200_multi* m, const uint64_t* in, uint64_t* out, size_t n, unsigned gens) {
+static int lifeb200_multi_step_batch_host_body(lifeb200_multi* m, const uint64_t* in, uint64_t* out, size_t n, unsigned gens) {
   if (!m) return set_error(LIFEB200_E_ARG, "null group");
   if (n == 0) return LIFEB200_OK;
   if (!in || !out) return set_error(LIFEB200_E_ARG, "null pattern pointer");
@@ -521,6 +521,34 @@ int lifeb200_multi_sync(lifeb200_multi* m) {
   for (lifeb200_ctx* c : m->ctx)
     if (int rc = lifeb200_sync(c)) return rc;
   return LIFEB200_OK;
+}
+
+int lifeb200_multi_create(const int* devices, int n_devices, lifeb200_multi** out) {
+  return guarded([&]() -> int { return lifeb200_multi_create_body(devices, n_devices, out); });
+}
+
+int lifeb200_multi_create_rank(int device, int rank, int world, const char* id128, lifeb200_multi** out) {
+  return guarded([&]() -> int { return lifeb200_multi_create_rank_body(device, rank, world, id128, out); });
+}
+
+int lifeb200_multi_reserve(lifeb200_multi* m, uint64_t n, size_t cap) {
+  return guarded([&]() -> int { return lifeb200_multi_reserve_body(m, n, cap); });
+}
+
+int lifeb200_multi_soup_survey(lifeb200_multi* m, uint64_t first_id, uint64_t n, uint64_t seed, int dist, unsigned gens,
+                               lifeb200_hit* hits, size_t cap, uint64_t* n_hits, uint64_t* pop_sum, uint64_t* hash_xor) {
+  return guarded([&]() -> int { return lifeb200_multi_soup_survey_body(m, first_id, n, seed, dist, gens, hits, cap, n_hits, pop_sum, hash_xor); });
+}
+
+int lifeb200_multi_enumerate_collisions(lifeb200_multi* m, const uint64_t* catalysts, unsigned n_catalysts,
+                                        const uint64_t* projectiles, unsigned n_projectiles, uint64_t id_begin,
+                                        uint64_t id_end, unsigned gens, unsigned stable_interval, lifeb200_hit* hits,
+                                        size_t cap, uint64_t* n_hits, uint64_t* n_skipped) {
+  return guarded([&]() -> int { return lifeb200_multi_enumerate_collisions_body(m, catalysts, n_catalysts, projectiles, n_projectiles, id_begin, id_end, gens, stable_interval, hits, cap, n_hits, n_skipped); });
+}
+
+int lifeb200_multi_step_batch_host(lifeb200_multi* m, const uint64_t* in, uint64_t* out, size_t n, unsigned gens) {
+  return guarded([&]() -> int { return lifeb200_multi_step_batch_host_body(m, in, out, n, gens); });
 }
 
 }  // extern "C"
