@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(kBlockC) interaction_offsets_kernel(const uint
 // The expressions follow the reference member term by term, including which `ignored` mask each operand carries
 // (its second and third terms mask the OTHER weld's operand with the first weld's zone: kept, parity is bit-exact).
 // Records are LifeWeld layouts: state, frozen2, frozen1, frozen0 (4 x 64 words).
-__global__ void __launch_bounds__(kBlockC) weld_interaction_offsets_kernel(const uint64_t* __restrict__ a, size_t n_a,
+__global__ void __launch_bounds__(kBlockC, 2) weld_interaction_offsets_kernel(const uint64_t* __restrict__ a, size_t n_a,
                                                                            const uint64_t* __restrict__ b, size_t n_b,
                                                                            uint64_t* __restrict__ out, size_t n) {
   const size_t p = ((size_t)blockIdx.x * kBlockC + threadIdx.x) >> 5;
