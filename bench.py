@@ -265,6 +265,119 @@ def _emit(line: dict):
         os.write(_JSON_FD, data)
 
 
+def run_single_process(args):
+    """`bench.py --gpus N` WITHOUT torchrun: one process drives N GPUs through the C library alone (lifeb200_multi_*:
+    ncclCommInitAll, one host thread per GPU inside the calls) -- no torch, no process group.  Same JSON line; the
+    resident figure steps every GPU's own 1 Mi soups from one Python thread per GPU (ctypes releases the GIL), timed
+    with CUDA events on each GPU's stream, max over GPUs."""
+    import threading as th
+
+    from lifeapi_b200 import HIT_DTYPE, MultiEngine
+    n_gpus, n, gens = args.gpus, args.soups, args.gens
+    group = MultiEngine(list(range(n_gpus)))
+    engs = [group.engine(i) for i in range(n_gpus)]
+    nbytes = n * 512
+    bufs = []
+    for i, e in enumerate(engs):
+        d_in, d_out = e.malloc(nbytes), e.malloc(nbytes)
+        e.soup_dev(d_in, i * n, n, SEED, 0)
+        e.sync()
+        bufs.append((d_in, d_out))
+    p_int, mhz_eff = engs[0].measure_int_peak()
+
+    def on_all(fn):
+        res = [None] * n_gpus
+        ts = [th.Thread(target=lambda i=i: res.__setitem__(i, fn(i))) for i in range(n_gpus)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        return res
+
+    def timed_steps(i, k):
+        e = engs[i]
+        e.timer_start()
+        for _ in range(k):
+            e.step_batch_dev(bufs[i][0], bufs[i][1], n, gens)
+        return e.timer_stop()
+
+    on_all(lambda i: timed_steps(i, args.warmup))
+    sampler = ClockSampler(0)
+    sampler.start()
+    ms = max(on_all(lambda i: timed_steps(i, args.steps)))
+    clocks = sampler.stop()
+    cells_all = float(n_gpus) * n * 4096.0 * gens
+    value = cells_all * args.steps / (ms * 1e-3) / 1e9
+    folds = on_all(lambda i: engs[i].fold_dev(bufs[i][1], n, i * n))
+    parity = [parity_against_cpu(engs[i], bufs[i][1], i * n, n, gens) for i in range(n_gpus)]
+    # e2e: one pinned host batch of N x n soups through lifeb200_multi_step_batch_host
+    e2e = None
+    if not args.no_e2e:
+        h_in = engs[0].host_alloc((n_gpus * n, 64))
+        h_out = engs[0].host_alloc((n_gpus * n, 64))
+        for i in range(n_gpus):
+            engs[i].d2h(h_in[i * n:(i + 1) * n], bufs[i][0])
+            engs[i].sync()
+        for _ in range(min(args.warmup, 2)):
+            group.step_batch_host(h_in, gens, out=h_out)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            group.step_batch_host(h_in, gens, out=h_out)
+        dt = time.perf_counter() - t0
+        ok = True
+        for i in range(n_gpus):
+            engs[i].h2d(bufs[i][1], h_out[i * n:(i + 1) * n])
+            ok = ok and engs[i].fold_dev(bufs[i][1], n, i * n) == folds[i]
+        e2e = {"value": cells_all * args.steps / dt / 1e9, "unit": UNIT, "h2d_bytes_per_step": nbytes * n_gpus,
+               "d2h_bytes_per_step": nbytes * n_gpus, "ms_per_step": dt / args.steps * 1e3, "host_memory": "pinned (lifeb200_host_alloc)",
+               "api": "lifeb200_multi_step_batch_host", "matches_resident_path": bool(ok)}
+        engs[0].host_free(h_in)
+        engs[0].host_free(h_out)
+    survey = None
+    if not args.no_survey:
+        total5, gens5 = args.survey_soups, 4096
+        hits = np.zeros(total5 // 8 + 4096, dtype=HIT_DTYPE)
+        group.reserve(total5, len(hits))
+        group.soup_survey(0, min(total5, n_gpus << 14), SEED, 0, 16, len(hits), hits=hits)
+        t0 = time.perf_counter()
+        merged, ps5, hx5 = group.soup_survey(0, total5, SEED, 0, gens5, len(hits), hits=hits)
+        t_total = time.perf_counter() - t0
+        lo = group.shard(0, total5, n_gpus - 1)[0]
+        m = min(1 << 16, total5 - lo)
+        own, _, _ = engs[0].soup_survey(lo, m, SEED, 0, gens5, m)
+        sel = (merged["id"] >= lo) & (merged["id"] < lo + m)
+        survey = {"workload": f"config5: ONE batch of {total5} on-device soups x {gens5} gens over {n_gpus} GPU(s) of this process",
+                  "api": "lifeb200_multi_create + lifeb200_multi_soup_survey", "nccl_version": group.info()["nccl_version"],
+                  "active_hits_total": int(len(merged)), "pop_sum": int(ps5), "hash_xor": f"{int(hx5):016x}", "total_s": t_total,
+                  "gather_ms_device": group.last_gather_ms(), "value": total5 * 4096.0 * gens5 / t_total / 1e9, "unit": UNIT,
+                  "cross_rank_parity": {"range": [int(lo), int(lo + m)], "owner_rank": n_gpus - 1, "records": int(sel.sum()),
+                                        "equal": bool(own.tobytes() == merged[sel].tobytes())}}
+    kernel_ms = ms / args.steps
+    exec_per32, exec_src = executed_instr_per_32_cells("step_kernel_x<8>")
+    per_gpu = n * 4096.0 * gens / (kernel_ms * 1e-3)
+    pop_sum = sum(f[0] for f in folds) & 0xFFFFFFFFFFFFFFFF
+    hash_xor = 0
+    for f in folds:
+        hash_xor ^= f[1]
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": kernel_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": dict(workload_config(args, n_gpus), launch="single process, lifeb200_multi_create (no torch, no process group)"),
+            "clocks": clocks, "e2e": e2e, "gpu_launches": args.steps * n_gpus,
+            "roofline": {"bound": "int_pipe", "unit": "T lane-instr/s (LOP3+SHF)", "peak": p_int / 1e12,
+                         "achieved": per_gpu * exec_per32 / 32.0 / 1e12, "frac": per_gpu * exec_per32 / 32.0 / p_int,
+                         "executed_instr_per_32_cells": exec_per32, "executed_source": exec_src, "traffic": None, "kernel": "step_kernel_x<8>",
+                         "kernel_ms": kernel_ms},
+            "cpu_baseline": None,
+            "parity": {"checked": sum(p["checked"] for p in parity), "equal": all(p["equal"] for p in parity), "vs": parity[0]["vs"],
+                       "what": f"the first {parity[0]['checked']} output patterns of every GPU against the reference's Step({gens})"},
+            "survey_gather": survey, "checksum": {"pop_sum": int(pop_sum), "hash_xor": f"{int(hash_xor):016x}"}}
+    _emit(line)
+    for i, e in enumerate(engs):
+        e.free(bufs[i][0])
+        e.free(bufs[i][1])
+    group.close()
+
+
 def main():
     args = parse_args()
     _claim_stdout()
@@ -274,6 +387,9 @@ def main():
 
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
+        return
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        run_single_process(args)  # one process, N GPUs, the C library's own multi-GPU group
         return
 
     import torch

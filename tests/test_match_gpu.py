@@ -213,3 +213,25 @@ def test_config5_real_shape_sample_and_prefix_vs_reference(engine, ref, port):
         _, a, b = engine.soup_survey(k << 21, 1 << 21, SEED, 0, gens, cap=1 << 21)
         ps, hx = ps + a, hx ^ b
     assert 0 < ps < pop_sum
+
+
+def test_config4_full_size_vs_reference(engine, ref):
+    """BASELINE config 4 at its full size: all 4 Mi placements (32 catalysts x 32 glider variants x 4096 offsets, <= 256
+    generations, stable_interval 8) -- EVERY hit record and the skipped count against the reference's own
+    Moved / ZOI / Step / Contains loop on all host threads (about half a minute of CPU)."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from bench_extras import D4, GLIDER, STILL_LIFES, _pattern
+    names = list(STILL_LIFES)
+    cats = np.stack([_pattern(STILL_LIFES[names[i % 8]], 28, 28, D4[(i // 8) * 2]) for i in range(32)])
+    g0 = np.stack([_pattern(GLIDER, 8, 8, tf) for tf in D4])
+    phases = [g0]
+    for _ in range(3):
+        phases.append(engine.step_batch_host(phases[-1], 1))
+    gliders = np.ascontiguousarray(np.stack(phases, axis=1).reshape(32, 64))
+    total = 32 * 32 * 4096
+    hits, skipped = engine.enumerate_collisions(cats, gliders, 0, total, 256, 8, 1 << 20)
+    ids, ff, rec, sk = ref.enumerate_mt(cats, gliders, 0, total, 256, 8, 1 << 20, 0)
+    assert skipped == sk and len(hits) == len(ids) > 1000
+    assert (hits["id"] == ids).all() and (hits["g_first_false"] == ff).all() and (hits["g_recovered"] == rec).all()
