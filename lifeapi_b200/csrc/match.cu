@@ -631,7 +631,7 @@ static void host_zoi(const uint64_t* s, uint64_t* out) {  // LifeAPI.hpp:521-536
 // match kernels keep three tiles (state, wanted&mask, mask) in registers: cap W at 16.
 // packing 4 placements costs about 6 generations of stepping
 // measured crossovers against the lane-group kernels (profiles/r01z_multi_thresholds.txt)
-constexpr unsigned kEnumerateMultiFrom = 16, kSurveyMultiFrom = 16, kStepMatchMultiFrom = 32;
+constexpr unsigned kEnumerateMultiFrom = 16, kSurveyMultiFrom = 16, kStepMatchMultiFrom = 8;
 static inline int match_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
 static inline int survey_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
 
@@ -824,7 +824,7 @@ int lifeb200_step_match_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const u
   if (int rc = ensure_dense(ctx, n)) return rc;
   uint64_t* dense = static_cast<uint64_t*>(ctx->d_dense);
   // many generations: 4 patterns per lane group in the row-class layout (step_match_kernel_x), unless the caller
-  // pinned the lane grouping or another layout; packing three planes of four patterns costs about 10 generations
+  // pinned the lane grouping or another layout; measured 14-18 % faster from 8 generations up (profiles/r02_thresholds.txt)
   const bool multi = ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kStepMatchMultiFrom));
   if (multi) {
     const size_t groups = (n + 3) / 4;

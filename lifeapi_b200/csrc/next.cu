@@ -305,8 +305,9 @@ static unsigned grid_hash(const lifeb200_ctx* ctx, size_t n) {
 
 extern "C" {
 
-// packing four planes of four records costs about 23 generations of the cheaper loop (5 x 12.5 instructions per register against 2.75 saved per generation)
-constexpr unsigned kWeldMultiFrom = 24;
+// measured crossover against the lane-group kernel (profiles/r02_thresholds.txt): level at 12 generations, +4 % at 16,
+// +19 % at 64, +21 % at 128
+constexpr unsigned kWeldMultiFrom = 12;
 static int launch_weld(lifeb200_ctx* ctx, cudaStream_t st, uint64_t* records, size_t n, unsigned gens) {
   if (ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kWeldMultiFrom))) {
     const size_t groups = (n + 3) / 4;
