@@ -12,7 +12,8 @@ Specs
               inputs s0, k0, s1, k1 (3x3 sum = s0 + 2 (k0 + s1) + 4 k1, centre included), cell, f0, f1, f2;
               output (T0 ^ T2) & (T1 ^ T2) & (cell | T0) with T = (sum + f) mod 8.  Rows: every (left, mid, right)
               column-count triple in 0..3 with cell <= [mid >= 1] and mid == 3 => cell, every f in 0..7.
-              csrc/next.cu uses 9 gates for it.
+              The ripple form is 9 gates; 8 were found (csrc/next.cu uses them).
+  weld_full   the same function from the raw column counts (10 inputs, 768 care rows); csrc/next.cu spends 12 gates.
 """
 import itertools
 import subprocess
@@ -45,7 +46,21 @@ def spec_weld_tail():
     return names, sorted(uniq.items())
 
 
-SPECS = {"weld_tail": spec_weld_tail}
+def spec_weld_full():
+    """The whole per-cell function of LifeWeld::Step from the three column counts (12 gates in csrc/next.cu: two full
+    adders + the 8-gate tail): inputs l0 l1 m0 m1 r0 r1 cell f0 f1 f2."""
+    rows = {}
+    for l, m, r in itertools.product(range(4), repeat=3):
+        for cell in (0, 1):
+            if (cell and m < 1) or (m == 3 and not cell):
+                continue
+            for f in range(8):
+                t = (l + m + r + f) & 7
+                rows[(l & 1, l >> 1, m & 1, m >> 1, r & 1, r >> 1, cell, f & 1, (f >> 1) & 1, f >> 2)] = int(t == 3 or (t == 4 and cell))
+    return ["l0", "l1", "m0", "m1", "r0", "r1", "cell", "f0", "f1", "f2"], sorted(rows.items())
+
+
+SPECS = {"weld_tail": spec_weld_tail, "weld_full": spec_weld_full}
 
 
 class Cnf:
