@@ -487,6 +487,24 @@ struct LifeHit {
 };
 static_assert(sizeof(LifeHit) == sizeof(lifeb200_hit), "hit record layout");
 
+// RAII page-lock of a caller-owned batch: LifeBatch::Step(batch, n) on a std::vector copies through pageable memory
+// (correct, but staged by the driver and not overlapped); pinning the vector's storage once makes every later host
+// call on it as fast as one on lifeb200_host_alloc memory.  The vector must not reallocate while pinned.
+class LifePinned {
+ public:
+  explicit LifePinned(std::vector<LifeState>& batch, lifeb200_ctx* ctx = nullptr)
+      : ctx_(ctx ? ctx : lifeb200::DefaultContext()), ptr_(batch.empty() ? nullptr : batch.data()) {
+    if (ptr_) lifeb200::Check(lifeb200_host_register(ctx_, ptr_, batch.size() * sizeof(LifeState)), "lifeb200_host_register");
+  }
+  ~LifePinned() { if (ptr_) lifeb200_host_unregister(ctx_, ptr_); }
+  LifePinned(const LifePinned&) = delete;
+  LifePinned& operator=(const LifePinned&) = delete;
+
+ private:
+  lifeb200_ctx* ctx_;
+  void* ptr_;
+};
+
 class LifeBatch {
  public:
   explicit LifeBatch(lifeb200_ctx* ctx = nullptr) : ctx_(ctx ? ctx : lifeb200::DefaultContext()) {}

@@ -72,6 +72,12 @@ int lifeb200_malloc(lifeb200_ctx* ctx, void** dptr, size_t bytes);
 int lifeb200_free(lifeb200_ctx* ctx, void* dptr);
 int lifeb200_host_alloc(lifeb200_ctx* ctx, void** hptr, size_t bytes); /* pinned */
 int lifeb200_host_free(lifeb200_ctx* ctx, void* hptr);
+/* Page-lock a host range the CALLER owns (a std::vector<LifeState>'s storage, a numpy array) so that the *_host calls
+ * copy from / to it asynchronously and overlap with the kernels, as they do for lifeb200_host_alloc memory; pinning
+ * costs about as much as one pageable copy of the range, so it pays for buffers that are used more than once.
+ * Unregister before the memory is freed. */
+int lifeb200_host_register(lifeb200_ctx* ctx, void* hptr, size_t bytes);
+int lifeb200_host_unregister(lifeb200_ctx* ctx, void* hptr);
 int lifeb200_memcpy_h2d(lifeb200_ctx* ctx, void* dst, const void* src, size_t bytes); /* async */
 int lifeb200_memcpy_d2h(lifeb200_ctx* ctx, void* dst, const void* src, size_t bytes); /* async */
 int lifeb200_memset(lifeb200_ctx* ctx, void* dst, int value, size_t bytes);           /* async */

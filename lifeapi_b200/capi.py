@@ -63,6 +63,8 @@ SIGNATURES = {
     "lifeb200_free": (C.c_int, [_vp, _vp]),
     "lifeb200_host_alloc": (C.c_int, [_vp, C.POINTER(_vp), C.c_size_t]),
     "lifeb200_host_free": (C.c_int, [_vp, _vp]),
+    "lifeb200_host_register": (C.c_int, [_vp, _vp, C.c_size_t]),
+    "lifeb200_host_unregister": (C.c_int, [_vp, _vp]),
     "lifeb200_memcpy_h2d": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "lifeb200_memcpy_d2h": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "lifeb200_memset": (C.c_int, [_vp, _vp, C.c_int, C.c_size_t]),
@@ -278,6 +280,13 @@ class Engine:
 
     def host_free(self, arr: np.ndarray) -> None:
         self._check(self.lib.lifeb200_host_free(self._h, arr.ctypes.data))
+
+    def host_register(self, arr: np.ndarray) -> None:
+        """Page-lock a caller-owned numpy array (lifeb200_host_register); pair with host_unregister(arr)."""
+        self._check(self.lib.lifeb200_host_register(self._h, arr.ctypes.data, arr.nbytes))
+
+    def host_unregister(self, arr: np.ndarray) -> None:
+        self._check(self.lib.lifeb200_host_unregister(self._h, arr.ctypes.data))
 
     def h2d(self, dptr: int, src: np.ndarray) -> None:
         self._check(self.lib.lifeb200_memcpy_h2d(self._h, dptr, _ptr(src), src.nbytes))

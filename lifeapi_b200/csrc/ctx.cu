@@ -202,6 +202,18 @@ int lifeb200_host_free(lifeb200_ctx* ctx, void* hptr) {
   if (hptr) LIFEB200_CUDA(cudaFreeHost(hptr));
   return LIFEB200_OK;
 }
+int lifeb200_host_register(lifeb200_ctx* ctx, void* hptr, size_t bytes) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (!hptr || bytes == 0) return set_error(LIFEB200_E_ARG, "null or empty host range");
+  LIFEB200_CUDA(cudaHostRegister(hptr, bytes, cudaHostRegisterPortable));
+  return LIFEB200_OK;
+}
+int lifeb200_host_unregister(lifeb200_ctx* ctx, void* hptr) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (!hptr) return set_error(LIFEB200_E_ARG, "null host pointer");
+  LIFEB200_CUDA(cudaHostUnregister(hptr));
+  return LIFEB200_OK;
+}
 int lifeb200_memcpy_h2d(lifeb200_ctx* ctx, void* dst, const void* src, size_t bytes) {
   LIFEB200_CHECK_CTX(ctx);
   if (bytes) LIFEB200_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));

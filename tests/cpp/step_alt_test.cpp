@@ -95,6 +95,13 @@ static void Batch_MatchesSingles() {
   std::vector<LifeState> host = batch;
   LifeBatch::Step(host, 64);
   EXPECT_TRUE(host == want);
+  {
+    std::vector<LifeState> pinned = batch;  // the same call on a page-locked vector (asynchronous, overlapped copies)
+    LifePinned lock(pinned);
+    LifeBatch::Step(pinned, 32);
+    LifeBatch::Step(pinned, 32);
+    EXPECT_TRUE(pinned == want);
+  }
   LifeBatch resident;
   resident.Upload(batch);
   resident.Step(32);

@@ -181,3 +181,24 @@ def test_weld_interaction_offsets_vs_reference(engine, ref, port):
     pc = cat.copy()
     pc[:, 1:] = 0
     assert (engine.weld_interaction_offsets_host(pc, plain) == ref.weld_interaction_offsets_batch(pc, plain, 0)).all()
+
+
+def test_host_register_caller_owned_buffer(engine, port):
+    """lifeb200_host_register: a caller-owned (numpy) batch is page-locked in place and stepped through the host
+    pipeline; same bytes as the pageable path, several pipeline chunks."""
+    n = 70_001
+    soups = port.soup(0, n, SEED, 0)
+    want = engine.step_batch_host(soups, 12)
+    mine = soups.copy()
+    out = np.empty_like(mine)
+    engine.host_register(mine)
+    engine.host_register(out)
+    try:
+        engine.step_batch_host(mine, 12, out=out)
+        assert (out == want).all()
+        engine.step_batch_host(out, 0, out=out)  # gens = 0 on a registered buffer, in place
+        assert (out == want).all()
+    finally:
+        engine.host_unregister(mine)
+        engine.host_unregister(out)
+    assert (want[:64] == port.step_batch(soups[:64], 12)).all()

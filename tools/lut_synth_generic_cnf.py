@@ -60,7 +60,45 @@ def spec_weld_full():
     return ["l0", "l1", "m0", "m1", "r0", "r1", "cell", "f0", "f1", "f2"], sorted(rows.items())
 
 
-SPECS = {"weld_tail": spec_weld_tail, "weld_full": spec_weld_full}
+def _lut(tt, a, b, c):
+    return (tt >> ((a << 2) | (b << 1) | c)) & 1
+
+
+def _three_valued(side):
+    """The hi-plane tail of the three-valued step FUSED with the combine (csrc/life_three.cuh): inputs = the 4-signal
+    pair code of the (state | unknown) plane, the far column's count there, that plane's centre cell, the lo plane's
+    (alive, A) signals and the centre's unknown bit; outputs next_on, next_unknown.  Today: 5-gate tail + 3-gate combine.
+    Rows: every 3 x 3 neighbourhood over {off, on, unknown} (disjoint planes), for the pair's left or right column."""
+    rows = {}
+    for cells in itertools.product(range(3), repeat=9):  # 0 off, 1 on, 2 unknown; column-major: far, own, other
+        col = [cells[0:3], cells[3:6], cells[6:9]]
+        far, own, other = col
+        centre = own[1]
+        cs = [sum(1 for v in c if v == 1) for c in (far, own, other)]   # lo plane (state)
+        ct = [sum(1 for v in c if v != 0) for c in (far, own, other)]   # hi plane (state | unknown)
+        cell_s, cell_t, u = int(centre == 1), int(centre != 0), int(centre == 2)
+        n_lo, n_hi = sum(cs), sum(ct)
+        alive = lambda n, c: int(n == 3 or (c and n == 4))  # noqa: E731
+        a_lo, al_lo = int(n_lo >= 3), alive(n_lo, cell_s)
+        a_hi, al_hi = int(n_hi >= 3), alive(n_hi, cell_t)
+        next_on = int((not u) and al_lo and al_hi)
+        next_unknown = int(u or (a_hi and not (a_lo and not al_lo) and not (al_lo and al_hi)))
+        # pair code of the hi plane: (a, b) = (left column of the pair, right column of the pair)
+        a, b = (ct[1], ct[2]) if side == "left" else (ct[2], ct[1])
+        a0, a1, b0, b1 = a & 1, a >> 1, b & 1, b >> 1
+        p0 = _lut(0x56, a0, b0, b1)
+        p1 = _lut(0xBE, a1, b1, p0)
+        p2 = _lut(0xE4, a1, b1, p0)
+        p3 = _lut(0x92, a0, b0, p1)
+        key = (p0, p1, p2, p3, ct[0] & 1, ct[0] >> 1, cell_t, al_lo, a_lo, u)
+        val = (next_on, next_unknown)
+        assert rows.setdefault(key, val) == val, "inconsistent rows: the inputs do not determine the outputs"
+    names = ["p0", "p1", "p2", "p3", "c0", "c1", "cell_t", "alive_lo", "A_lo", "u"]
+    return names, sorted(rows.items())
+
+
+SPECS = {"weld_tail": spec_weld_tail, "weld_full": spec_weld_full,
+         "three_hi_left": lambda: _three_valued("left"), "three_hi_right": lambda: _three_valued("right")}
 
 
 class Cnf:
@@ -98,8 +136,8 @@ def build(names, rows, gates):
         if g > 0:  # every gate but the first must be used later or be the output: weak pruning, skip
             pass
         lut = [cnf.var() for _ in range(8)]
-        last = g == gates - 1
-        if not last:
+        n_out = len(rows[0][1]) if isinstance(rows[0][1], tuple) else 1
+        if g < gates - n_out:
             cnf.add(-lut[0])
         out = [cnf.var() for _ in range(n_rows)]
         for r in range(n_rows):
@@ -117,8 +155,11 @@ def build(names, rows, gates):
                 pre = [(-x[k] if bits[k] else x[k]) for k in range(3)]
                 cnf.add(*pre, -lut[idx], out[r])
                 cnf.add(*pre, lut[idx], -out[r])
-            if last:
-                cnf.add(out[r] if rows[r][1] else -out[r])
+            want = rows[r][1] if isinstance(rows[r][1], tuple) else (rows[r][1],)
+            k_out = len(want)
+            if g >= gates - k_out:  # the last k gates are the outputs, in order
+                w = want[g - (gates - k_out)]
+                cnf.add(out[r] if w else -out[r])
         sig.append([("v", out[r]) for r in range(n_rows)])
         meta.append((sel, lut))
     return cnf, meta
