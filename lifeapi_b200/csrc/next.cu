@@ -49,32 +49,31 @@ __global__ void __launch_bounds__(kBlockN, 1) weld_step_kernel(uint64_t* __restr
 // The state lives in registers exactly as in step_kernel_x<8> (64 registers per lane, 1/4 shift per register and
 // generation).  The three frozen planes are constants of the launch and do not fit beside it (64 + 192), so every
 // lane packs them once and parks them in shared memory (768 B per lane, [48][128] uint4 per CTA: a warp's LDS.128
-// reads 32 consecutive uint4, conflict-free) and reads them back every generation: 48 LDS.128 against ~910 integer
-// instructions.  Per 32 cells and generation: 2 LOP3 column count + 1/4 SHF + 12 LOP3 (14.25).  What is computed:
+// reads 32 consecutive uint4, conflict-free) and reads them back every generation: 48 LDS.128 against ~850 integer
+// instructions.  Per 32 cells and generation: 2 LOP3 column count + 1/4 SHF + 11 LOP3 (13.25).  What is computed:
 //   s0, k0 = full adder of the three low count bits; s1, k1 = of the three high ones        (sum = s0 + 2 (k0 + s1) + 4 k1)
 //   T0 = s0 ^ f0, c0 = s0 & f0; x = k0 ^ s1; T1 = x ^ f1 ^ c0, c1 = maj(x, f1, c0); S2 = k1 ^ (k0 & s1); T2 = S2 ^ f2 ^ c1
 //   next = (T0 ^ T2) & (cell | T0) & (T1 ^ T2)          -- bit3 of the count and the last carry dropped, as the reference does
-// (9 gates as written; weld_rule below evaluates the same function in 8)
+// (9 gates as written; weld_rule below evaluates the same function in 7)
 // A warp whose 16 records have no frozen cell at all (LifeWeld(state), LifeWeld.hpp:24-25) runs the plain step.
 constexpr int kWeldXSmem = 128 * 48 * 16;
 
-// The tail after the two full adders is an 8-gate network from exact synthesis (tools/lut_synth_generic_cnf.py weld_tail 8,
-// 76 minutes of z3; the ripple form above is 9 gates, tools/synth_logs/weld_tail_{8,9}.txt).  It uses the count's
-// don't-cares -- the cell is the middle bit of its own column's triple, so cell = 1 implies a count >= 1 there and a
-// count of 3 implies cell = 1 -- and is checked on every reachable (left, mid, right, cell, frozen) in
-// tests/test_oracle.py::test_weld_rule_luts_exhaustive.
+// The tail after the two full adders is a 7-gate network from exact synthesis (tools/lut_synth_generic_cnf.py weld_tail 7,
+// 82 minutes of z3; the ripple form above is 9 gates, an 8-gate network took 76 minutes, tools/synth_logs/weld_tail_*.txt).
+// It uses the count's don't-cares -- the cell is the middle bit of its own column's triple, so cell = 1 implies a
+// count >= 1 there and a count of 3 implies cell = 1 -- and is checked on every reachable (left, mid, right, cell,
+// frozen) in tests/test_oracle.py::test_weld_rule_luts_exhaustive.
 __device__ __forceinline__ uint32_t weld_rule(uint32_t l0, uint32_t l1, uint32_t m0, uint32_t m1, uint32_t r0, uint32_t r1,
                                               uint32_t cell, uint32_t f2, uint32_t f1, uint32_t f0) {
   const uint32_t s0 = lop3<kXor3>(l0, m0, r0), k0 = lop3<kMaj>(l0, m0, r0);
   const uint32_t s1 = lop3<kXor3>(l1, m1, r1), k1 = lop3<kMaj>(l1, m1, r1);
-  const uint32_t g0 = lop3<0x96>(k0, s1, f1);
-  const uint32_t g1 = lop3<0x7E>(k0, s1, g0);
-  const uint32_t g2 = cell ^ f2;
-  const uint32_t g3 = lop3<0x96>(k1, g1, g2);
-  const uint32_t g4 = lop3<0x96>(f2, g2, g3);
-  const uint32_t g5 = lop3<0x7C>(s0, f0, g3);
-  const uint32_t g6 = lop3<0x5E>(g0, g3, g5);
-  return lop3<0x44>(g2, g4, g6);
+  const uint32_t g0 = lop3<0xDA>(s0, cell, f0);
+  const uint32_t g1 = lop3<0x96>(k0, s1, f1);
+  const uint32_t g2 = lop3<0x98>(cell, g0, g1);
+  const uint32_t g3 = lop3<0x56>(s1, f1, f2);
+  const uint32_t g4 = lop3<0x86>(k0, g1, g2);
+  const uint32_t g5 = lop3<0x48>(k1, g2, g3);
+  return lop3<0x6A>(g0, g4, g5);
 }
 
 __global__ void __launch_bounds__(128, 2) weld_step_kernel_x(uint64_t* records, size_t n, unsigned gens) {
