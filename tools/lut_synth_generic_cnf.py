@@ -97,7 +97,21 @@ def _three_valued(side):
     return names, sorted(rows.items())
 
 
-SPECS = {"weld_tail": spec_weld_tail, "weld_full": spec_weld_full,
+def spec_life_col():
+    """One column of the plain B3/S23 step from the three binary column counts and the centre cell, no sharing with the
+    neighbouring column: a (left), b (own, contains the cell), c (right).  The step kernel spends 11 gates per column
+    PAIR; two unshared columns of 5 gates each would beat it."""
+    rows = {}
+    for a, b, c in itertools.product(range(4), repeat=3):
+        for cell in (0, 1):
+            if (cell and b < 1) or (b == 3 and not cell):
+                continue
+            n = a + b + c
+            rows[(a & 1, a >> 1, b & 1, b >> 1, c & 1, c >> 1, cell)] = int(n == 3 or (cell and n == 4))
+    return ["a0", "a1", "b0", "b1", "c0", "c1", "cell"], sorted(rows.items())
+
+
+SPECS = {"weld_tail": spec_weld_tail, "weld_full": spec_weld_full, "life_col": spec_life_col,
          "three_hi_left": lambda: _three_valued("left"), "three_hi_right": lambda: _three_valued("right")}
 
 
