@@ -64,6 +64,10 @@ def test_no_cpu_fallback_without_gpu(lib):
     with pytest.raises(LifeB200Error) as ei:
         Engine(0)
     assert ei.value.code in (E_NODEVICE, E_CUDA)
+    from lifeapi_b200 import MultiEngine
+    with pytest.raises(LifeB200Error) as ei:
+        MultiEngine([0])  # the multi-GPU group has no fallback either
+    assert ei.value.code in (E_NODEVICE, E_CUDA)
     # null-context compute call is an argument error, never a silent success
     rc = lib.lifeb200_step_batch_dev(None, None, None, 1, 1)
     assert rc != 0 and lib.lifeb200_last_error()
