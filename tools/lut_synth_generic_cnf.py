@@ -176,6 +176,11 @@ def build(names, rows, gates):
                 cnf.add(out[r] if w else -out[r])
         sig.append([("v", out[r]) for r in range(n_rows)])
         meta.append((sel, lut))
+    # symmetry breaking: every gate that is not an output feeds some later gate
+    n_out = len(rows[0][1]) if isinstance(rows[0][1], tuple) else 1
+    for g in range(gates - n_out):
+        users = [meta[h][0][k][n_in + g] for h in range(g + 1, gates) for k in range(3)]
+        cnf.add(*users)
     return cnf, meta
 
 
