@@ -349,9 +349,9 @@ def next_rows(eng, p_int):
         ms = _time(eng, lambda: eng._check(eng.lib.lifeb200_weld_step_batch_dev(eng._h, d, n, gens)))
         out["weld_step"] = {"workload": f"LifeWeld::Step x {gens} generations on {n} records (2048 B each), in place, dense random frozen planes", "ms": ms,
                             "value": n * 4096.0 * gens / (ms * 1e-3) / 1e9, "unit": "Gcell/s",
-                            "executed": "13.25 int-pipe instr per 32 cells per generation (weld_step_kernel_x, profiles/r02_sass_mix.txt) "
+                            "executed": "12.25 int-pipe instr per 32 cells per generation (weld_step_kernel_x, profiles/r02_sass_mix.txt) "
                                         "+ about 62 per 32 cells per launch for the five plane conversions",
-                            "pipe_utilisation": n * 4096.0 * (gens * 13.25 + 62.5) / 32.0 / (ms * 1e-3) / p_int}
+                            "pipe_utilisation": n * 4096.0 * (gens * 12.25 + 62.5) / 32.0 / (ms * 1e-3) / p_int}
         if ref is not None:
             m = 1 << 14
             t0 = time.perf_counter()

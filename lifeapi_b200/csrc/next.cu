@@ -14,7 +14,27 @@ namespace lifeb200 {
 
 constexpr int kBlockN = 256;
 static inline unsigned grid_n(size_t n, int lpp) { return (unsigned)((n * (size_t)lpp + kBlockN - 1) / kBlockN); }
-// ---- LifeWeld::Step: 3x3 count (bit3 dropped, as the reference does) + frozen count, then the rule ----
+// The tail after the two full adders is a 6-gate network from exact synthesis (tools/lut_synth_generic_cnf.py weld_tail 6;
+// the ripple form above is 9 gates; z3 found 8 gates in 76 minutes, 7 in 82, 6 in 27, tools/synth_logs/weld_tail_*.txt).
+// g0, g1 are the full adder of the weight-2 bits (k0, s1, f1), g4 the weight-4 sum bit; g2 and g3 fold the weight-1
+// bits, the cell and the rule together, using the count's don't-cares -- the cell is the middle bit of its own column's
+// triple, so cell = 1 implies a count >= 1 there and a count of 3 implies cell = 1.  Checked on every reachable
+// (left, mid, right, cell, frozen) in tests/test_oracle.py::test_weld_rule_luts_exhaustive.
+__device__ __forceinline__ uint32_t weld_rule(uint32_t l0, uint32_t l1, uint32_t m0, uint32_t m1, uint32_t r0, uint32_t r1,
+                                              uint32_t cell, uint32_t f2, uint32_t f1, uint32_t f0) {
+  const uint32_t s0 = lop3<kXor3>(l0, m0, r0), k0 = lop3<kMaj>(l0, m0, r0);
+  const uint32_t s1 = lop3<kXor3>(l1, m1, r1), k1 = lop3<kMaj>(l1, m1, r1);
+  const uint32_t g0 = lop3<kXor3>(k0, s1, f1);
+  const uint32_t g1 = lop3<kMaj>(k0, s1, f1);
+  const uint32_t g2 = lop3<0xDA>(s0, cell, f0);
+  const uint32_t g3 = lop3<0x98>(cell, g0, g2);
+  const uint32_t g4 = lop3<kXor3>(k1, f2, g1);
+  return lop3<0x48>(g2, g3, g4);
+}
+
+// ---- LifeWeld::Step, lane groups in the reference layout (launches of fewer than 12 generations): the column counts
+// of the walk below feed weld_rule directly -- 2 SHF + 2 + 10 LOP3 = 14 per 32 cells (18 with the four count planes and
+// the ripple adder of round 1).
 template <int LPP>
 __global__ void __launch_bounds__(kBlockN, 1) weld_step_kernel(uint64_t* __restrict__ records, size_t n, unsigned gens) {
   constexpr int W = Tile<LPP>::W;
@@ -29,17 +49,21 @@ __global__ void __launch_bounds__(kBlockN, 1) weld_step_kernel(uint64_t* __restr
 #pragma unroll
     for (int w = 0; w < W; w++) s.lo[w] = s.hi[w] = f2.lo[w] = f2.hi[w] = f1.lo[w] = f1.hi[w] = f0.lo[w] = f0.hi[w] = 0;
   }
+  const int up_src = sub + LPP - 1, dn_src = sub + 1;
 #pragma unroll 1
   for (unsigned g = 0; g < gens; g++) {
-    Tile<LPP> b3, b2, b1, b0;
-    s.neighbour_count(sub, b3, b2, b1, b0);
+    const Cnt first = count_rows(s.lo[0], s.hi[0]);
+    const Cnt last = (W == 1) ? first : count_rows(s.lo[W - 1], s.hi[W - 1]);
+    Cnt prev = halo<LPP>(last, up_src);
+    const Cnt after = halo<LPP>(first, dn_src);
+    Cnt cur = first;
 #pragma unroll
-    for (int k = 0; k < 2 * W; k++) {
-      const uint32_t sum0 = reg(b0, k) ^ reg(f0, k), c0 = reg(b0, k) & reg(f0, k);        // HalfAdd
-      const uint32_t sum1 = lop3<kXor3>(reg(b1, k), reg(f1, k), c0), c1 = lop3<kMaj>(reg(b1, k), reg(f1, k), c0);
-      const uint32_t sum2 = lop3<kXor3>(reg(b2, k), reg(f2, k), c1);                     // carry2 unused
-      const uint32_t t = (sum0 ^ sum2) & (sum1 ^ sum2);
-      reg(s, k) = t & (reg(s, k) | sum0);
+    for (int w = 0; w < W; w++) {
+      const Cnt next = (w == W - 1) ? after : (w + 1 == W - 1) ? last : count_rows(s.lo[w + 1], s.hi[w + 1]);
+      s.lo[w] = weld_rule(prev.b0lo, prev.b1lo, cur.b0lo, cur.b1lo, next.b0lo, next.b1lo, s.lo[w], f2.lo[w], f1.lo[w], f0.lo[w]);
+      s.hi[w] = weld_rule(prev.b0hi, prev.b1hi, cur.b0hi, cur.b1hi, next.b0hi, next.b1hi, s.hi[w], f2.hi[w], f1.hi[w], f0.hi[w]);
+      prev = cur;
+      cur = next;
     }
   }
   if (valid) s.store(records + p * 4 * kN, sub);
@@ -49,32 +73,14 @@ __global__ void __launch_bounds__(kBlockN, 1) weld_step_kernel(uint64_t* __restr
 // The state lives in registers exactly as in step_kernel_x<8> (64 registers per lane, 1/4 shift per register and
 // generation).  The three frozen planes are constants of the launch and do not fit beside it (64 + 192), so every
 // lane packs them once and parks them in shared memory (768 B per lane, [48][128] uint4 per CTA: a warp's LDS.128
-// reads 32 consecutive uint4, conflict-free) and reads them back every generation: 48 LDS.128 against ~850 integer
-// instructions.  Per 32 cells and generation: 2 LOP3 column count + 1/4 SHF + 11 LOP3 (13.25).  What is computed:
+// reads 32 consecutive uint4, conflict-free) and reads them back every generation: 48 LDS.128 against ~790 integer
+// instructions.  Per 32 cells and generation: 2 LOP3 column count + 1/4 SHF + 10 LOP3 (12.25).  What is computed:
 //   s0, k0 = full adder of the three low count bits; s1, k1 = of the three high ones        (sum = s0 + 2 (k0 + s1) + 4 k1)
 //   T0 = s0 ^ f0, c0 = s0 & f0; x = k0 ^ s1; T1 = x ^ f1 ^ c0, c1 = maj(x, f1, c0); S2 = k1 ^ (k0 & s1); T2 = S2 ^ f2 ^ c1
 //   next = (T0 ^ T2) & (cell | T0) & (T1 ^ T2)          -- bit3 of the count and the last carry dropped, as the reference does
-// (9 gates as written; weld_rule below evaluates the same function in 7)
+// (9 gates as written; weld_rule below evaluates the same function in 6)
 // A warp whose 16 records have no frozen cell at all (LifeWeld(state), LifeWeld.hpp:24-25) runs the plain step.
 constexpr int kWeldXSmem = 128 * 48 * 16;
-
-// The tail after the two full adders is a 7-gate network from exact synthesis (tools/lut_synth_generic_cnf.py weld_tail 7,
-// 82 minutes of z3; the ripple form above is 9 gates, an 8-gate network took 76 minutes, tools/synth_logs/weld_tail_*.txt).
-// It uses the count's don't-cares -- the cell is the middle bit of its own column's triple, so cell = 1 implies a
-// count >= 1 there and a count of 3 implies cell = 1 -- and is checked on every reachable (left, mid, right, cell,
-// frozen) in tests/test_oracle.py::test_weld_rule_luts_exhaustive.
-__device__ __forceinline__ uint32_t weld_rule(uint32_t l0, uint32_t l1, uint32_t m0, uint32_t m1, uint32_t r0, uint32_t r1,
-                                              uint32_t cell, uint32_t f2, uint32_t f1, uint32_t f0) {
-  const uint32_t s0 = lop3<kXor3>(l0, m0, r0), k0 = lop3<kMaj>(l0, m0, r0);
-  const uint32_t s1 = lop3<kXor3>(l1, m1, r1), k1 = lop3<kMaj>(l1, m1, r1);
-  const uint32_t g0 = lop3<0xDA>(s0, cell, f0);
-  const uint32_t g1 = lop3<0x96>(k0, s1, f1);
-  const uint32_t g2 = lop3<0x98>(cell, g0, g1);
-  const uint32_t g3 = lop3<0x56>(s1, f1, f2);
-  const uint32_t g4 = lop3<0x86>(k0, g1, g2);
-  const uint32_t g5 = lop3<0x48>(k1, g2, g3);
-  return lop3<0x6A>(g0, g4, g5);
-}
 
 __global__ void __launch_bounds__(128, 2) weld_step_kernel_x(uint64_t* records, size_t n, unsigned gens) {
   constexpr int M = 8, P = 4;

@@ -28,7 +28,7 @@ def test_committed_sass_histogram_matches_the_shipped_library(fresh_mix):
     g = fresh_mix["step_kernel_x<8>"]["generation_loop"]
     assert g["ops"]["LOP3"] == 480 and g["ops"]["SHF"] == 16 and g["ops"]["SHFL"] == 32 and g["instructions"] == 531
     assert fresh_mix["step_kernel_x<8>"]["alu_instr_per_32_cells"] == 7.75
-    assert fresh_mix["weld_step_kernel_x"]["alu_instr_per_32_cells"] == 13.25
+    assert fresh_mix["weld_step_kernel_x"]["alu_instr_per_32_cells"] == 12.25
 
 
 def test_no_kernel_spills(fresh_mix):

@@ -303,7 +303,7 @@ def test_port_unknown_step_sop_vs_reference_and_semantics(port, ref):
 
 
 def test_weld_rule_luts_exhaustive():
-    """weld_rule in csrc/next.cu (LifeWeld::Step in layout 8): two full adders over the column counts, then the 7-gate
+    """weld_rule in csrc/next.cu (LifeWeld::Step in layout 8): two full adders over the column counts, then the 6-gate
     tail from exact synthesis.  Checked against LifeWeld.hpp:169-186 -- next = [T == 3] | cell & [T == 4] with
     T = (3x3 sum + frozen) mod 8 -- on every (left, mid, right) column count, cell and frozen value a record can produce."""
     import os
@@ -311,7 +311,7 @@ def test_weld_rule_luts_exhaustive():
     from conftest import ROOT
     src = open(os.path.join(ROOT, "lifeapi_b200", "csrc", "next.cu")).read()
     body = src[src.index("uint32_t weld_rule("):src.index("weld_step_kernel_x(uint64_t* records")]
-    assert re.findall(r"lop3<(\w+)>", body) == ["kXor3", "kMaj", "kXor3", "kMaj", "0xDA", "0x96", "0x98", "0x56", "0x86", "0x48", "0x6A"]
+    assert re.findall(r"lop3<(\w+)>", body) == ["kXor3", "kMaj", "kXor3", "kMaj", "kXor3", "kMaj", "0xDA", "0x98", "kXor3", "0x48"]
     checked = 0
     for l in range(4):
         for m in range(4):
@@ -323,14 +323,13 @@ def test_weld_rule_luts_exhaustive():
                     s1, k1 = _lop3(0x96, l >> 1, m >> 1, r >> 1), _lop3(0xE8, l >> 1, m >> 1, r >> 1)
                     for f in range(8):
                         f0, f1, f2 = f & 1, (f >> 1) & 1, f >> 2
-                        g0 = _lop3(0xDA, s0, cell, f0)
-                        g1 = _lop3(0x96, k0, s1, f1)
-                        g2 = _lop3(0x98, cell, g0, g1)
-                        g3 = _lop3(0x56, s1, f1, f2)
-                        g4 = _lop3(0x86, k0, g1, g2)
-                        g5 = _lop3(0x48, k1, g2, g3)
+                        g0 = _lop3(0x96, k0, s1, f1)
+                        g1 = _lop3(0xE8, k0, s1, f1)
+                        g2 = _lop3(0xDA, s0, cell, f0)
+                        g3 = _lop3(0x98, cell, g0, g2)
+                        g4 = _lop3(0x96, k1, f2, g1)
                         t = (l + m + r + f) & 7
-                        assert _lop3(0x6A, g0, g4, g5) == int(t == 3 or (t == 4 and cell)), (l, m, r, cell, f)
+                        assert _lop3(0x48, g2, g3, g4) == int(t == 3 or (t == 4 and cell)), (l, m, r, cell, f)
                         checked += 1
     assert checked == 64 * 2 * 8 - 2 * 16 * 8
 
