@@ -72,7 +72,7 @@ def test_weld_and_interaction_vs_oracle(engine, port, lpp):
 
 
 def test_weld_step_every_kernel_vs_reference(engine, ref, port):
-    """LifeWeld::Step through both kernels -- 4 records per lane group in the row-class layout (default from 12
+    """LifeWeld::Step through both kernels -- 4 records per lane group in the row-class layout (default from 24
     generations, or layout 8 pinned) and the lane-group kernel (layout 1 / pinned lanes) -- on dense frozen planes
     (every carry of the 3-bit add exercised), on sparse ones, and on records with no frozen cell (the plain-step
     fast path); ragged batch sizes around the 4-record group."""
