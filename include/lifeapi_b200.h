@@ -138,6 +138,23 @@ int lifeb200_step_match_host(lifeb200_ctx* ctx, const uint64_t* patterns, const 
                              const uint32_t* target_index, size_t n, size_t n_targets, uint64_t first_id, unsigned gens,
                              unsigned stable_interval, lifeb200_hit* hits, size_t cap, uint64_t* n_hits);
 
+/* Allocation-free variant of lifeb200_step_match_dev.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same hit records in the same order; the call (and everything it
+ * enqueues) performs no cudaMalloc / cudaFree / allocating library call, on any invocation including the first.
+ * Its scratch (8 bytes per pattern of dense results + the per-tile counts of the ordered compaction) is a file-scope
+ * `static __device__ __align__(256)` array in csrc/match.cu of LIFEB200_STEP_MATCH_STATIC_MAX patterns (2 MiB + 1 KiB),
+ * which every GPU that loads the library holds until exit; its device address is taken once per device with
+ * cudaGetSymbolAddress.  n > LIFEB200_STEP_MATCH_STATIC_MAX is rejected with LIFEB200_E_ARG (split the batch, or
+ * use lifeb200_step_match_dev).  EVERY call on a device shares that one array and it keeps the previous call's
+ * contents (nothing in it has to start at zero: each call overwrites the words it reads): two calls that overlap on
+ * the same GPU -- different contexts or streams -- RACE; serialise them (one stream, or events). */
+#define LIFEB200_STEP_MATCH_STATIC_MAX 262144u
+int lifeb200_step_match_static_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const uint64_t* targets,
+                                   const uint32_t* target_index, size_t n, uint64_t first_id, unsigned gens,
+                                   unsigned stable_interval, lifeb200_hit* hits, size_t cap,
+                                   unsigned long long* n_hits);
+
 /* ---- A11  LifeState::Contains(const LifeTarget&, int dx, int dy) (LifeTarget.hpp:38-42 -> LifeAPI.hpp:399-422):
  * contains[p] = 1 iff targets[p] (or the one shared target, n_targets == 1) placed at offset (dx, dy) fits
  * states[p]: every wanted cell ON and every unwanted cell OFF in state word (i + dx) & 63 rotated right by dy. */

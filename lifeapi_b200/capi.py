@@ -78,6 +78,8 @@ SIGNATURES = {
     "lifeb200_neighbour_count_host": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "lifeb200_step_match_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_uint64, C.c_uint, C.c_uint, _vp,
                                           C.c_size_t, _vp]),
+    "lifeb200_step_match_static_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_uint64, C.c_uint, C.c_uint, _vp,
+                                                 C.c_size_t, _vp]),
     "lifeb200_step_match_host": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_size_t, C.c_uint64, C.c_uint, C.c_uint, _vp,
                                            C.c_size_t, _u64p]),
     "lifeb200_contains_target_batch_dev": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, C.c_int, C.c_int, _vp]),
@@ -326,6 +328,13 @@ class Engine:
                        d_n_hits) -> None:
         self._check(self.lib.lifeb200_step_match_dev(self._h, _ptr(d_patterns), _ptr(d_targets), _ptr(d_target_index), n,
                                                      first_id, gens, stable_interval, _ptr(d_hits), cap, _ptr(d_n_hits)))
+
+    def step_match_static_dev(self, d_patterns, d_targets, d_target_index, n, first_id, gens, stable_interval, d_hits, cap,
+                              d_n_hits) -> None:
+        """lifeb200_step_match_static_dev: the same call on the library's static device scratch (no allocation)."""
+        self._check(self.lib.lifeb200_step_match_static_dev(self._h, _ptr(d_patterns), _ptr(d_targets), _ptr(d_target_index),
+                                                            n, first_id, gens, stable_interval, _ptr(d_hits), cap,
+                                                            _ptr(d_n_hits)))
 
     def step_match(self, patterns: np.ndarray, targets: np.ndarray, target_index: np.ndarray | None, gens: int,
                    stable_interval: int, first_id: int = 0, cap: int | None = None) -> np.ndarray:

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdlib>
+#include <mutex>
 #include <vector>
 
 #include "ctx.h"
@@ -867,6 +868,76 @@ int lifeb200_step_match_host(lifeb200_ctx* ctx, const uint64_t* patterns, const 
   LIFEB200_CUDA(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
   LIFEB200_CUDA(cudaStreamSynchronize(ctx->stream));
   return download_hits(ctx, d_hits, cap, hits, n_hits);
+}
+
+// ---- allocation-free variant of lifeb200_step_match_dev (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops) ---
+// The dense per-id results and the per-tile counts of the ordered compaction live in a file-scope __device__ array
+// instead of the context's grow-only cudaMalloc scratch.  Every GPU that loads the library holds the array
+// (2 MiB + 1 KiB) until exit.  In host code the array's NAME is a host-side stand-in, not a device address: the
+// address is taken once per device, with that device current, by cudaGetSymbolAddress below.
+constexpr size_t kStaticMaxIds = LIFEB200_STEP_MATCH_STATIC_MAX;
+constexpr size_t kStaticMaxTiles = (kStaticMaxIds + kCompactTile - 1) / kCompactTile;
+static __device__ __align__(256) unsigned long long g_static_match_scratch[kStaticMaxIds + kStaticMaxTiles];
+
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mu;
+static unsigned long long* g_static_addr[kStaticMaxDevices];  // per device, nullptr until that device's first call
+
+static int static_scratch_for(const lifeb200_ctx* ctx, unsigned long long** out) {
+  if (ctx->device < 0 || ctx->device >= kStaticMaxDevices)
+    return set_error(LIFEB200_E_ARG, "static scratch: device ordinal %d outside 0..%d", ctx->device, kStaticMaxDevices - 1);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_addr[ctx->device]) {
+    void* p = nullptr;  // the context's device is current here (LIFEB200_CHECK_CTX)
+    LIFEB200_CUDA(cudaGetSymbolAddress(&p, g_static_match_scratch));
+    if (!p) return set_error(LIFEB200_E_CUDA, "cudaGetSymbolAddress returned a null address");
+    g_static_addr[ctx->device] = static_cast<unsigned long long*>(p);
+  }
+  *out = g_static_addr[ctx->device];
+  return LIFEB200_OK;
+}
+
+int lifeb200_step_match_static_dev(lifeb200_ctx* ctx, const uint64_t* patterns, const uint64_t* targets,
+                                   const uint32_t* target_index, size_t n, uint64_t first_id, unsigned gens,
+                                   unsigned stable_interval, lifeb200_hit* hits, size_t cap, unsigned long long* n_hits) {
+  LIFEB200_CHECK_CTX(ctx);
+  if (!n_hits) return set_error(LIFEB200_E_ARG, "null n_hits");
+  if (stable_interval == 0) return set_error(LIFEB200_E_ARG, "stable_interval must be >= 1");
+  if (n > kStaticMaxIds)
+    return set_error(LIFEB200_E_ARG, "lifeb200_step_match_static_dev: n = %llu patterns exceeds the static scratch "
+                     "(LIFEB200_STEP_MATCH_STATIC_MAX = %llu); split the batch or use lifeb200_step_match_dev",
+                     (unsigned long long)n, (unsigned long long)kStaticMaxIds);
+  LIFEB200_CUDA(cudaMemsetAsync(n_hits, 0, sizeof(unsigned long long), ctx->stream));
+  if (n == 0) return LIFEB200_OK;
+  if (!patterns || !targets || (!hits && cap)) return set_error(LIFEB200_E_ARG, "null pointer");
+  if (!aligned16(patterns) || !aligned16(targets)) return set_error(LIFEB200_E_ARG, "pointers must be 16-byte aligned");
+  unsigned long long* scratch = nullptr;
+  if (int rc = static_scratch_for(ctx, &scratch)) return rc;
+  // nothing here must start at zero: every id in [0, n) writes its dense word, every tile its count, and the scan
+  // writes *n_hits; words beyond n keep the previous call's contents and are never read
+  uint64_t* dense = reinterpret_cast<uint64_t*>(scratch);
+  unsigned long long* tiles = scratch + kStaticMaxIds;
+  const bool multi = ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kStepMatchMultiFrom));
+  if (multi) {
+    const size_t groups = (n + 3) / 4;
+    LIFEB200_CUDA(cudaFuncSetAttribute(step_match_kernel_x, cudaFuncAttributeMaxDynamicSharedMemorySize, kEnumXSmem));
+    step_match_kernel_x<<<(unsigned)((groups * 8 + 127) / 128), 128, kEnumXSmem, ctx->stream>>>(
+        patterns, targets, target_index, n, gens, stable_interval, dense);
+  } else {
+    int lpp = match_lpp(ctx);
+    LIFEB200_DISPATCH_LPP_MIN4(lpp, (step_match_kernel<LPP><<<grid_m(n, LPP), kBlockM, 0, ctx->stream>>>(
+                                        patterns, targets, target_index, n, gens, stable_interval, dense)));
+  }
+  LIFEB200_LAUNCHED(ctx);
+  const size_t n_tiles = (n + kCompactTile - 1) / kCompactTile;
+  compact_count_kernel<<<(unsigned)n_tiles, kCompactThreads, 0, ctx->stream>>>(dense, n, tiles);
+  LIFEB200_LAUNCHED(ctx);
+  compact_scan_kernel<<<1, 1024, 0, ctx->stream>>>(tiles, n_tiles, n_hits);
+  LIFEB200_LAUNCHED(ctx);
+  compact_scatter_kernel<<<(unsigned)n_tiles, kCompactThreads, 0, ctx->stream>>>(dense, n, tiles, first_id, hits, cap);
+  LIFEB200_LAUNCHED(ctx);
+  return LIFEB200_OK;
 }
 
 static int enumerate_args(const uint64_t* catalysts, unsigned n_catalysts, const uint64_t* projectiles,
