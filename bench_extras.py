@@ -350,8 +350,8 @@ def next_rows(eng, p_int):
         out["weld_step"] = {"workload": f"LifeWeld::Step x {gens} generations on {n} records (2048 B each), in place, dense random frozen planes", "ms": ms,
                             "value": n * 4096.0 * gens / (ms * 1e-3) / 1e9, "unit": "Gcell/s",
                             "executed": "12.25 int-pipe instr per 32 cells per generation (weld_step_kernel_x, profiles/r02_sass_mix.txt) "
-                                        "+ about 62 per 32 cells per launch for the five plane conversions",
-                            "pipe_utilisation": n * 4096.0 * (gens * 12.25 + 62.5) / 32.0 / (ms * 1e-3) / p_int}
+                                        "+ about 55 per 32 cells per launch for the five plane conversions",
+                            "pipe_utilisation": n * 4096.0 * (gens * 12.25 + 55.0) / 32.0 / (ms * 1e-3) / p_int}
         if ref is not None:
             m = 1 << 14
             t0 = time.perf_counter()

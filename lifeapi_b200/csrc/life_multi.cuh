@@ -24,14 +24,6 @@ __device__ __forceinline__ void exchange_bits(uint32_t& a, uint32_t& b, int d, u
   b ^= t;
   a ^= t << d;
 }
-// position index bits (p4 p3 p2) = (y4 y3 y5) <-> (y5 y4 y3): swap p2 / p3 (nibbles 1 and 2 of every halfword),
-// then p3 / p4 (bytes 1 and 2).  Either order undoes the other: both steps are involutions and pack / unpack
-// apply them mirrored.  2 SHF + 2 LOP3 + 1 PRMT.
-__device__ __forceinline__ uint32_t swap_nibbles_1_2(uint32_t v) {
-  const uint32_t t = ((v >> 4) ^ v) & 0x00F000F0u;
-  return v ^ t ^ (t << 4);
-}
-
 template <int M>
 struct TileX {
   static_assert(M == 4 || M == 8, "row classes per column");
@@ -88,11 +80,12 @@ struct TileX {
   __device__ __forceinline__ void pack(int c, const uint64_t (&w)[P]) {
     if constexpr (M == 8) {
       // A permutation of index bits: the 8 input registers are numbered (s1 s0 y5) and hold position (y4 .. y0);
-      // the output registers are numbered (y2 y1 y0) and hold position (y5 y4 y3 s1 s0).  Three register <->
-      // position exchanges (s1 <-> y1, s0 <-> y0, y5 <-> y2) put every bit into its register at position
-      // (y4 y3 y5 s1 s0); one nibble swap and one byte swap rotate the top three index bits.  100 integer
-      // instructions per column (12.5 per register) where the 8x8 transposes + byte gathers + two perfect
-      // shuffles per register took about 400.
+      // the output registers are numbered (y2 y1 y0) and hold position (y5 y4 y3 s1 s0).  Four register <->
+      // position exchanges (s1 <-> y1, s0 <-> y0, then the register bit that starts as y5 trades places with
+      // position bit 3 and then with position bit 2: it walks y5 -> y3 -> y2 while the position becomes
+      // (y4 y5 y3 s1 s0)) and one byte swap (position bits 4 <-> 3) per register.  88 integer instructions per
+      // column (11 per register; 100 with three exchanges + a nibble swap + the byte swap, round 1) where the
+      // 8x8 transposes + byte gathers + two perfect shuffles per register took about 400.
       uint32_t x[P][2];
 #pragma unroll
       for (int s = 0; s < P; s++) { x[s][0] = (uint32_t)w[s]; x[s][1] = (uint32_t)(w[s] >> 32); }
@@ -104,11 +97,14 @@ struct TileX {
         exchange_bits(x[2][h], x[3][h], 1, 0x55555555u);
       }
 #pragma unroll
-      for (int s = 0; s < P; s++) exchange_bits(x[s][0], x[s][1], 4, 0x0F0F0F0Fu);  // y5 <-> y2
+      for (int s = 0; s < P; s++) {
+        exchange_bits(x[s][0], x[s][1], 8, 0x00FF00FFu);  // y5 <-> y3: position (y4 y5 y2 s1 s0), register bit h = y3
+        exchange_bits(x[s][0], x[s][1], 4, 0x0F0F0F0Fu);  // y3 <-> y2: position (y4 y5 y3 s1 s0), register bit h = y2
+      }
 #pragma unroll
       for (int h = 0; h < 2; h++)
 #pragma unroll
-        for (int s = 0; s < P; s++) r[c][4 * h + s] = __byte_perm(swap_nibbles_1_2(x[s][h]), 0, 0x3120);
+        for (int s = 0; s < P; s++) r[c][4 * h + s] = __byte_perm(x[s][h], 0, 0x3120);  // bytes 1 <-> 2: (y5 y4 y3 s1 s0)
     } else {
       // M = 4, P = 2: rows 4j+k.  Per pattern: unshuffle twice brings bit 4j+k of each 32-bit half to
       // bit 8k + j (byte k); byte k of the low half = rows 4j+k for j < 8, of the high half for j >= 8.
@@ -134,9 +130,12 @@ struct TileX {
 #pragma unroll
       for (int h = 0; h < 2; h++)
 #pragma unroll
-        for (int s = 0; s < P; s++) x[s][h] = swap_nibbles_1_2(__byte_perm(r[c][4 * h + s], 0, 0x3120));
+        for (int s = 0; s < P; s++) x[s][h] = __byte_perm(r[c][4 * h + s], 0, 0x3120);
 #pragma unroll
-      for (int s = 0; s < P; s++) exchange_bits(x[s][0], x[s][1], 4, 0x0F0F0F0Fu);
+      for (int s = 0; s < P; s++) {
+        exchange_bits(x[s][0], x[s][1], 4, 0x0F0F0F0Fu);
+        exchange_bits(x[s][0], x[s][1], 8, 0x00FF00FFu);
+      }
 #pragma unroll
       for (int h = 0; h < 2; h++) {
         exchange_bits(x[0][h], x[1][h], 1, 0x55555555u);

@@ -13,6 +13,9 @@ Specs
               output (T0 ^ T2) & (T1 ^ T2) & (cell | T0) with T = (sum + f) mod 8.  Rows: every (left, mid, right)
               column-count triple in 0..3 with cell <= [mid >= 1] and mid == 3 => cell, every f in 0..7.
               The ripple form is 9 gates; 8 were found (csrc/next.cu uses them).
+  weld_tail_rK  weld_tail with the frozen count RECODED: the three frozen planes are constants of a launch, so the kernel
+              may park ANY K functions of (f0, f1, f2) instead of the bits themselves (K = 3, 4); the solver chooses
+              them (8 free truth-table bits per plane, plane value at f = 0 fixed to 0: a complement folds into the LUTs).
   weld_full   the same function from the raw column counts (10 inputs, 768 care rows); csrc/next.cu spends 12 gates.
 """
 import itertools
@@ -44,6 +47,17 @@ def spec_weld_tail():
         assert uniq.setdefault(ins, out) == out, "inconsistent care rows"
     names = ["s0", "k0", "s1", "k1", "cell", "f0", "f1", "f2"]
     return names, sorted(uniq.items())
+
+
+def spec_weld_tail_recoded(k):
+    """weld_tail with K free planes F0..F(K-1) of the frozen count f: their row entries are ('f', f) and build() gives
+    every plane one variable per value of f."""
+    names, rows = spec_weld_tail()
+    out = {}
+    for ins, o in rows:
+        f = ins[5] | (ins[6] << 1) | (ins[7] << 2)
+        out[ins[:5] + tuple(("f", f) for _ in range(k))] = o
+    return names[:5] + [f"F{p}" for p in range(k)], sorted(out.items(), key=lambda kv: str(kv[0]))
 
 
 def spec_weld_full():
@@ -111,7 +125,7 @@ def spec_life_col():
     return ["a0", "a1", "b0", "b1", "c0", "c1", "cell"], sorted(rows.items())
 
 
-SPECS = {"weld_tail": spec_weld_tail, "weld_full": spec_weld_full, "life_col": spec_life_col,
+SPECS = {"weld_tail": spec_weld_tail, "weld_tail_r3": lambda: spec_weld_tail_recoded(3), "weld_tail_r4": lambda: spec_weld_tail_recoded(4), "weld_full": spec_weld_full, "life_col": spec_life_col,
          "three_hi_left": lambda: _three_valued("left"), "three_hi_right": lambda: _three_valued("right")}
 
 
@@ -136,7 +150,15 @@ class Cnf:
 def build(names, rows, gates):
     cnf = Cnf()
     n_in, n_rows = len(names), len(rows)
-    sig = [[("c", rows[r][0][i]) for r in range(n_rows)] for i in range(n_in)]  # per signal: per-row constant or variable
+    sig = []  # per signal: per-row constant or variable
+    free = {}  # input index -> its 8 variables (one per value of the recoded quantity)
+    for i in range(n_in):
+        if isinstance(rows[0][0][i], tuple):
+            free[i] = [cnf.var() for _ in range(8)]
+            cnf.add(-free[i][0])
+            sig.append([("v", free[i][rows[r][0][i][1]]) for r in range(n_rows)])
+        else:
+            sig.append([("c", rows[r][0][i]) for r in range(n_rows)])
     meta = []
     for g in range(gates):
         m = len(sig)
@@ -181,6 +203,7 @@ def build(names, rows, gates):
     for g in range(gates - n_out):
         users = [meta[h][0][k][n_in + g] for h in range(g + 1, gates) for k in range(3)]
         cnf.add(*users)
+    cnf.free = free
     return cnf, meta
 
 
@@ -219,6 +242,8 @@ def main():
     print(f"{spec} gates={gates}: {status} in {dt:.0f} s", flush=True)
     if status == "sat":
         labels = list(names)
+        for i, vs in sorted(cnf.free.items()):
+            print(f"  {names[i]}(f = 0..7) = {[int(v in model) for v in vs]}")
         for g, (sel, lut) in enumerate(meta):
             ops = [labels[[i for i, v in enumerate(sel[k]) if v in model][0]] for k in range(3)]
             tt = sum(1 << idx for idx in range(8) if lut[idx] in model)
