@@ -576,7 +576,7 @@ def main():
     hbm_src = "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
 
     per_gpu_cells_s = n * 4096.0 * gens / (kernel_ms * 1e-3)
-    layout8 = (args.layout in (0, 8)) and args.lpp == 0 and gens >= 20
+    layout8 = (args.layout in (0, 8)) and args.lpp == 0 and gens >= 16
     exec_per32, exec_src = executed_instr_per_32_cells("step_kernel_x<8>") if layout8 else (None, {"note": "non-default kernel"})
     traffic, traffic_file = ncu_dram_traffic() if (n, gens) == (N_SOUPS, GENS) and layout8 else (None, None)
     achieved_exec = per_gpu_cells_s * (exec_per32 / 32.0) if exec_per32 else None

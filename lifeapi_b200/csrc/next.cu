@@ -310,9 +310,10 @@ static unsigned grid_hash(const lifeb200_ctx* ctx, size_t n) {
 
 extern "C" {
 
-// measured crossover against the lane-group kernel, both with the 6-gate rule (profiles/r02_thresholds_weld_6gate.txt):
-// level at 24 generations, +4 % at 32, +9 % at 64, +11 % at 128 (the lane-group kernel needs no layout conversion)
-constexpr unsigned kWeldMultiFrom = 24;
+// measured crossover against the lane-group kernel, both with the 6-gate rule and the 11-instruction pack
+// (profiles/r02x_thresholds.txt): level at 16 generations, +2.5 % at 20, +7 % at 32, +10 % at 64, +11 % at 128 (the
+// lane-group kernel needs no layout conversion)
+constexpr unsigned kWeldMultiFrom = 18;
 static int launch_weld(lifeb200_ctx* ctx, cudaStream_t st, uint64_t* records, size_t n, unsigned gens) {
   if (ctx->lpp == 0 && (ctx->step_layout == 8 || (ctx->step_layout == 0 && gens >= kWeldMultiFrom))) {
     const size_t groups = (n + 3) / 4;

@@ -20,11 +20,11 @@ constexpr int kStepBlock = 128;
 //   1 = the reference's (rows 0..31 | 32..63): 2 shifts per register and generation, no conversion
 //   2 = even | odd rows: 1 shift per register; 4, 8 = rows by class mod 4 / 8 with 2 / 4 patterns
 //   bit-interleaved per register: 1/2, 1/4 shift per register.  The conversions after the load and before
-//   the store cost about 4 (layout 2) or 3 (layout 8: three register <-> position bit exchanges, life_multi.cuh)
-//   generations' worth of work, so auto picks by gens.  Measured crossovers (profiles/r01z_step_sweep.txt): layout 8
-//   beats the reference layout from about 20 generations and layout 2 everywhere; layout 2 is what a pinned lane
+//   the store cost about 4 (layout 2) or 3 (layout 8: four register <-> position bit exchanges, life_multi.cuh)
+//   generations' worth of work, so auto picks by gens.  Measured crossovers (profiles/r02x_step_sweep.txt): layout 8
+//   beats the reference layout from about 15 generations (1.099 against 1.119 ms at 16) and layout 2 everywhere; layout 2 is what a pinned lane
 //   grouping (lifeb200_set_lanes_per_pattern) falls back to.
-constexpr unsigned kInterleaveFrom = 36, kMultiFrom = 20;
+constexpr unsigned kInterleaveFrom = 36, kMultiFrom = 16;
 
 // Each warp owns 32/LPP whole patterns; `gens` generations run in registers between one
 // 128-bit vectorised load and one 128-bit vectorised store per 16 bytes of state.
