@@ -60,6 +60,16 @@ def spec_weld_tail_recoded(k):
     return names[:5] + [f"F{p}" for p in range(k)], sorted(out.items(), key=lambda kv: str(kv[0]))
 
 
+def spec_weld_full_recoded(k):
+    """weld_full with K free planes of the frozen count (see spec_weld_tail_recoded)."""
+    names, rows = spec_weld_full()
+    out = {}
+    for ins, o in rows:
+        f = ins[7] | (ins[8] << 1) | (ins[9] << 2)
+        out[ins[:7] + tuple(("f", f) for _ in range(k))] = o
+    return names[:7] + [f"F{p}" for p in range(k)], sorted(out.items(), key=lambda kv: str(kv[0]))
+
+
 def spec_weld_full():
     """The whole per-cell function of LifeWeld::Step from the three column counts (12 gates in csrc/next.cu: two full
     adders + the 8-gate tail): inputs l0 l1 m0 m1 r0 r1 cell f0 f1 f2."""
@@ -125,7 +135,8 @@ def spec_life_col():
     return ["a0", "a1", "b0", "b1", "c0", "c1", "cell"], sorted(rows.items())
 
 
-SPECS = {"weld_tail": spec_weld_tail, "weld_tail_r3": lambda: spec_weld_tail_recoded(3), "weld_tail_r4": lambda: spec_weld_tail_recoded(4), "weld_full": spec_weld_full, "life_col": spec_life_col,
+SPECS = {"weld_tail": spec_weld_tail, "weld_tail_r3": lambda: spec_weld_tail_recoded(3), "weld_tail_r4": lambda: spec_weld_tail_recoded(4),
+         "weld_full_r3": lambda: spec_weld_full_recoded(3), "weld_full": spec_weld_full, "life_col": spec_life_col,
          "three_hi_left": lambda: _three_valued("left"), "three_hi_right": lambda: _three_valued("right")}
 
 
