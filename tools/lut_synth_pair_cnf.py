@@ -13,6 +13,11 @@ per column finish  next = [T_x + T_x+1 + T_far == 3] | cell & [.. == 4].  Cost p
       LUT constants and wiring) and use the don't-cares each has: the cell is the middle bit of
       its own column's triple, so cell=1 implies T_own >= 1 and T_own = 3 implies cell = 1.
 
+--weld  the LifeWeld::Step rule instead (LifeWeld.hpp:169-186): every tail row also carries the cell's frozen count
+        f in 0..7 and  next = [T == 3] | cell & [T == 4]  with T = (sum + f) mod 8.  The tails read three FREE planes
+        F0..F2 of f (launch constants: the kernel may park any three functions of the frozen planes; 8 truth-table
+        bits per plane chosen by the solver, value at f = 0 fixed to 0).  Today: 2 x (4 + 6) LOP3 per column pair.
+
 Gate g reads three earlier signals (selector variables, strictly increasing indices); code gates
 may read the four count bits and earlier code gates, tail gates the far count, the cell, every
 code gate and earlier gates of the same tail.  Prints the netlist of a model, or UNSAT.
@@ -51,11 +56,13 @@ class Cnf:
             f.write(" ".join(map(str, c)) + " 0\n")
 
 
-def build(code, GP, GT, dc, raw=False, GTR=None):
+def build(code, GP, GT, dc, raw=False, GTR=None, weld=False):
     enc = CODES[code]
     cnf = Cnf()
     pair_rows = list(itertools.product(range(4), range(4)))            # (ca, cb)
     tail_rows = list(itertools.product(range(4), range(4), range(4), (0, 1)))  # (ca, cb, co, cell)
+    fvals = range(8) if weld else (0,)
+    free = {}  # (tag, plane) -> 8 variables
 
     # signal = ("const", [bits per row]) or ("var", [vars per row]); code signals live on pair rows,
     # tail signals on tail rows (code signals are looked up through the row's (ca, cb))
@@ -114,7 +121,8 @@ def build(code, GP, GT, dc, raw=False, GTR=None):
 
     def synth_tail(tag, rows, own, GT=GT):
         """own = 0: the cell belongs to column a (left), 1: to column b (right), None: no don't-cares."""
-        idx_pair = [pair_rows.index((ca, cb)) for ca, cb, co, cell in rows]
+        rows = [(ca, cb, co, cell, f) for ca, cb, co, cell in rows for f in fvals]
+        idx_pair = [pair_rows.index((ca, cb)) for ca, cb, co, cell, f in rows]
 
         def value(sig, r):
             kind, v, dom = sig
@@ -123,17 +131,23 @@ def build(code, GP, GT, dc, raw=False, GTR=None):
                 return ("c", v[rr]) if kind == "const" else ("v", v[rr])
             return ("c", v[r]) if kind == "const" else ("v", v[r])
 
-        cands = [("C0", ("const", [enc[co][0] for ca, cb, co, cell in rows], "tail")),
-                 ("C1", ("const", [enc[co][1] for ca, cb, co, cell in rows], "tail")),
-                 ("cell", ("const", [cell for ca, cb, co, cell in rows], "tail"))]
+        cands = [("C0", ("const", [enc[co][0] for ca, cb, co, cell, f in rows], "tail")),
+                 ("C1", ("const", [enc[co][1] for ca, cb, co, cell, f in rows], "tail")),
+                 ("cell", ("const", [cell for ca, cb, co, cell, f in rows], "tail"))]
+        if weld:
+            for pl in range(3):
+                fv = [cnf.var() for _ in range(8)]
+                cnf.add(-fv[0])
+                free[(tag, pl)] = fv
+                cands.append((f"F{pl}", ("var", [fv[f] for ca, cb, co, cell, f in rows], "tail")))
         cands += [(n, (s[0], s[1], "pair")) for n, s in (code_sigs if raw else code_gate_sigs)]
         last = None
         for g in range(GT):
             s = make_gate(f"{tag}{g}", list(cands), len(rows), value, g == GT - 1)
             cands.append((f"{tag}{g}", (s[0], s[1], "tail")))
             last = s
-        for r, (ca, cb, co, cell) in enumerate(rows):
-            n = ca + cb + co
+        for r, (ca, cb, co, cell, f) in enumerate(rows):
+            n = (ca + cb + co + f) & 7
             want = int(n == 3 or (cell and n == 4))
             cnf.add(last[1][r] if want else -last[1][r])
 
@@ -163,6 +177,7 @@ def build(code, GP, GT, dc, raw=False, GTR=None):
                 i = cands2.index(name)
                 users += [sel2[k][i] for k in range(3)]
         cnf.add(*users)
+    cnf.free = free
     return cnf, gates
 
 
@@ -203,12 +218,15 @@ def main():
         timeout = float(sys.argv[sys.argv.index("--timeout") + 1])
     raw = "--raw" in sys.argv
     gtr = int(sys.argv[sys.argv.index("--gtr") + 1]) if "--gtr" in sys.argv else None
-    cnf, gates = build(code, GP, GT, dc, raw, gtr)
+    weld = "--weld" in sys.argv
+    cnf, gates = build(code, GP, GT, dc, raw, gtr, weld)
     t0 = time.time()
     status, model = solve(cnf, timeout)
     dt = time.time() - t0
-    print(f"code {code} GP {GP} GT {GT} GTR {gtr} dc {dc} raw {raw}: vars {cnf.n} clauses {len(cnf.clauses)} -> {status} in {dt:.1f}s", flush=True)
+    print(f"{'weld ' if weld else ''}code {code} GP {GP} GT {GT} GTR {gtr} dc {dc} raw {raw}: vars {cnf.n} clauses {len(cnf.clauses)} -> {status} in {dt:.1f}s", flush=True)
     if model:
+        for (tag, pl), fv in sorted(cnf.free.items()):
+            print(f"  {tag}: F{pl}(f = 0..7) = {[int(model.get(v, False)) for v in fv]}")
         for name, cands, sel, lut in gates:
             ins = [cands[[model.get(v, False) for v in sel[k]].index(True)] for k in range(3)]
             lutv = sum(1 << i for i in range(8) if model.get(lut[i], False))
