@@ -36,7 +36,7 @@ INSTR_PER_CELL = 12.0 / 32.0  # algorithmic 2 SHF + 10 LOP3 per 
 # library (profiles/r02_sass_mix.json, made by tools/sass_mix.py from `cuobjdump -sass`); 7.75 is the fallback.
 # DRAM traffic of one launch is read from the committed `ncu --set full` capture of this launch shape.
 SASS_MIX_FILES = ["profiles/r02_sass_mix.json"]
-NCU_RAW_FILES = ["profiles/r02_step_kernel_x8_raw.csv", "profiles/r01z_step_kernel_x8_raw.csv"]
+NCU_RAW_FILES = ["profiles/r02v_step_kernel_x8_raw.csv", "profiles/r02_step_kernel_x8_raw.csv", "profiles/r01z_step_kernel_x8_raw.csv"]
 
 
 def executed_instr_per_32_cells(kernel="step_kernel_x<8>"):
