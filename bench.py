@@ -60,9 +60,10 @@ def ncu_dram_traffic(kernel_substr="step_kernel_x<8>", grid="(16384, 1, 1)"):
             hdr = rows[0]
             ik, ig = hdr.index("Kernel Name"), hdr.index("Grid Size")
             ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}  # rows[1] = units (ncu --print-units)
             for r in rows[2:]:
                 if kernel_substr in r[ik] and r[ig] == grid:
-                    return int(float(r[ir])) + int(float(r[iw])), rel
+                    return int(float(r[ir]) * scale[rows[1][ir]] + float(r[iw]) * scale[rows[1][iw]]), rel
         except Exception:  # noqa: BLE001
             continue
     return None, None
