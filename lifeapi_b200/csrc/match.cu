@@ -631,8 +631,9 @@ static void host_zoi(const uint64_t* s, uint64_t* out) {  // LifeAPI.hpp:521-536
 
 // match kernels keep three tiles (state, wanted&mask, mask) in registers: cap W at 16.
 // packing 4 placements costs about 6 generations of stepping
-// measured crossovers against the lane-group kernels (profiles/r01z_multi_thresholds.txt)
-constexpr unsigned kEnumerateMultiFrom = 16, kSurveyMultiFrom = 16, kStepMatchMultiFrom = 8;
+// measured crossovers against the lane-group kernels (profiles/r02x_multi_thresholds.txt; enumeration: level at 8
+// generations, 6 % ahead at 16)
+constexpr unsigned kEnumerateMultiFrom = 12, kSurveyMultiFrom = 16, kStepMatchMultiFrom = 8;
 static inline int match_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
 static inline int survey_lpp(const lifeb200_ctx* ctx) { return std::max(4, effective_lpp(ctx)); }
 
