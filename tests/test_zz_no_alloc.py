@@ -98,3 +98,22 @@ def test_static_scratch_rejects_sizes_beyond_the_maximum(engine):
         assert e.value.code == E_ARG and "LIFEB200_STEP_MATCH_STATIC_MAX" in str(e.value)
     finally:
         engine.free(d)
+
+
+def test_static_scratch_is_shared_by_every_context_of_the_device(engine, port):
+    """The array belongs to the device, not to a lifeb200_ctx: a second context on the same GPU (its own stream) uses the
+    same address, taken once; calls made one after the other from different contexts agree with the existing entry point."""
+    from lifeapi_b200 import Engine
+    c = golden("collisions.npz")
+    targets = np.ascontiguousarray(c["targets"], dtype=np.uint64)
+    ids = np.random.default_rng(23).choice(c["enum_ids"], 257, replace=False)
+    pats, tidx = _placements(port, c, ids)
+    n_ref, ref = _run(engine, engine.step_match_dev, pats, targets, tidx, 128, 8, 5, len(ids))
+    other = Engine(0)
+    try:
+        n_b, got_b = _run(other, other.step_match_static_dev, pats, targets, tidx, 128, 8, 5, len(ids))
+    finally:
+        other.close()
+    n_a, got_a = _run(engine, engine.step_match_static_dev, pats, targets, tidx, 128, 8, 5, len(ids))
+    assert n_a == n_b == n_ref > 100
+    assert got_a.tobytes() == ref.tobytes() and got_b.tobytes() == ref.tobytes()
